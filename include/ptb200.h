@@ -1,0 +1,253 @@
+/* ptb200.h — C ABI of the B200-native render hot path for programmerjake/path-trace.
+ *
+ * This is the drop-in boundary.  The reference has no FFI: the seam its
+ * render path sits behind is the C++ virtual interface
+ *     Object::makeSpanIterator()            (reference include/object.h:10-24)
+ *     SpanIterator::{init,next,isAtEnd,*}   (reference include/span.h:129-171)
+ *     traceRay / tracePixel                 (reference include/path-trace.h:58-207)
+ * driven by one caller, RenderBlock / BlockRenderer (reference src/test.cpp:310-518).
+ * The host C++ scene classes (path-trace_b200/host/ptb200_scene.hpp: same class names and
+ * constructors as the reference) flatten an Object graph into the plain arrays below and call
+ * these entry points.  Nothing here throws; every function returns 0 on success or a negative
+ * PTB_E* code, with ptb200_last_error() holding a thread-local message.  No torch / C++ types
+ * cross this boundary: plain pointers and sizes only.
+ *
+ * All float arithmetic on the device is IEEE binary32, like the reference.
+ */
+#ifndef PTB200_H_INCLUDED
+#define PTB200_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PTB200_ABI_VERSION 1
+
+/* ---- status codes -------------------------------------------------------------------------- */
+enum {
+    PTB_OK = 0,
+    PTB_EINVAL = -1,  /* bad argument / malformed scene program                                  */
+    PTB_ECUDA = -2,   /* CUDA runtime error (message has cudaGetErrorString)                     */
+    PTB_ENOMEM = -3,  /* host or device allocation failed                                        */
+    PTB_ENODEV = -4,  /* no CUDA device: the product path has no CPU fallback and fails loudly   */
+    PTB_EBUSY = -5    /* an asynchronous render is still running on this scene                   */
+};
+
+/* ---- flattened scene ("linear SoA CSG program") -------------------------------------------- */
+
+/* primitive kinds: reference src/sphere.cpp:31-49, src/plane.cpp:35-63 */
+enum { PTB_PRIM_SPHERE = 0, PTB_PRIM_PLANE = 1 };
+
+typedef struct PtbPrim {
+    float p[4];       /* sphere: centre.xyz, r*r (float product, reference src/sphere.cpp:10)      */
+                      /* plane : normal.xyz (as given, NOT normalised), d                          */
+    int32_t type;     /* PTB_PRIM_*                                                                */
+    int32_t material; /* index into materials[]                                                    */
+    int32_t chain;    /* index into chains[] = stack of TransformedObject wrappers, -1 = none      */
+    int32_t reserved;
+} PtbPrim;
+
+/* One TransformedObject (reference include/object.h:26-98).  Matrix element order is the
+ * reference's Matrix member order x00,x10,x20,x30, x01,x11,x21,x31, x02,x12,x22,x32
+ * (include/transform.h:19-21).  m maps the parent-space ray into the child's space
+ * (include/transform.h:429-432); inv = m.inverse() maps child normals back
+ * (include/span.h:122-127). */
+typedef struct PtbXform {
+    float m[12];
+    float inv[12];
+} PtbXform;
+
+/* chain_xf[first .. first+count) lists xform indices, OUTERMOST wrapper first. */
+typedef struct PtbChain {
+    int32_t first;
+    int32_t count;
+} PtbChain;
+
+/* Postfix CSG program, one uint32 per op: low 8 bits = kind, high 24 bits = argument.
+ * PUSH_PRIM pushes the (0- or 1-span) list of primitive <arg>; UNION / DIFFERENCE /
+ * INTERSECTION pop list B then list A and push the merge, using exactly the streaming merge
+ * rules of reference src/union.cpp:84-134, src/difference.cpp:84-135,
+ * src/intersection.cpp:84-130 (quirks included). */
+enum { PTB_OP_PUSH_PRIM = 0, PTB_OP_UNION = 1, PTB_OP_DIFFERENCE = 2, PTB_OP_INTERSECTION = 3 };
+#define PTB_OP(kind, arg) ((uint32_t)(kind) | ((uint32_t)(arg) << 8))
+#define PTB_OP_KIND(op) ((op) & 0xFFu)
+#define PTB_OP_ARG(op) ((op) >> 8)
+
+/* Texture programs.  Every reference wrapper texture has exactly one delegate, so a texture is
+ * a linear chain of wrapper ops ending in one leaf op, stored outermost-first in texops[].
+ * A texture is named by the index of its first op. */
+enum {
+    /* leaves */
+    PTB_TEX_CONST = 0,        /* ColorTexture              include/texture.h:29-58; data: r,g,b      */
+    PTB_TEX_IMAGE = 1,        /* ImageTexture              include/image_texture.h:9-35; arg: image  */
+    PTB_TEX_IMAGE_ALPHA = 2,  /* ImageAlphaTexture         include/image_texture.h:37-70             */
+    PTB_TEX_SKYBOX = 3,       /* ImageSkyboxTexture        include/image_texture.h:72-115; arg: first
+                                 of 6 consecutive images top,bottom,left,right,front,back            */
+    PTB_TEX_SKYBOX_ALPHA = 4, /* ImageSkyboxAlphaTexture   include/image_texture.h:117-181           */
+    /* wrappers */
+    PTB_TEX_AFFINE = 8,       /* TransformedTexture        include/texture.h:60-90; data: 12 floats  */
+    PTB_TEX_MULTIPLY = 9,     /* MultiplyTexture           include/filter_texture.h:30-47; data rgb  */
+    PTB_TEX_LOG = 10,         /* LogTexture                include/filter_texture.h:50-73            */
+    PTB_TEX_MIRRORBALL = 11,  /* MirrorBallSkymapTexture   include/transform_texture.h:35-59         */
+    PTB_TEX_SPHERICAL = 12    /* SphericalCoordinatesSkymapTexture include/transform_texture.h:61-86 */
+};
+#define PTB_TEX_IS_LEAF(kind) ((kind) < 8)
+
+typedef struct PtbTexOp {
+    int32_t kind; /* PTB_TEX_*                                               */
+    int32_t arg;  /* offset into texdata[] (floats) or image index           */
+} PtbTexOp;
+
+/* Material (reference include/material.h:10-37): five textures + ior. */
+enum { PTB_MAT_REFLECT = 0, PTB_MAT_SCATTER = 1, PTB_MAT_EMISSIVE = 2, PTB_MAT_TRANSMIT = 3, PTB_MAT_TRC = 4 };
+typedef struct PtbMaterial {
+    int32_t tex[5]; /* texture roots, PTB_MAT_* order */
+    float ior;
+    int32_t reserved[2];
+} PtbMaterial;
+
+/* RGBA float image, row 0 first, as reference Image (include/image.h:48-99). */
+typedef struct PtbImageDesc {
+    const float *rgba;
+    int32_t width, height;
+} PtbImageDesc;
+
+typedef struct PtbSceneDesc {
+    uint32_t abi_version; /* PTB200_ABI_VERSION */
+    int32_t n_prims, n_xforms, n_chains, n_chain_xf, n_ops, n_materials, n_texops, n_texdata, n_images;
+    const PtbPrim *prims;
+    const PtbXform *xforms;
+    const PtbChain *chains;
+    const int32_t *chain_xf;
+    const uint32_t *ops;
+    const PtbMaterial *materials;
+    const PtbTexOp *texops;
+    const float *texdata;
+    const PtbImageDesc *images;
+} PtbSceneDesc;
+
+typedef struct PtbScene PtbScene; /* opaque; immutable after create, shareable between threads */
+
+/* ---- ray-batch intersection (BASELINE config 3) --------------------------------------------- */
+
+enum { PTB_HIT_MISS = 0, PTB_HIT_ENTER = 1 /* hit a span start */, PTB_HIT_EXIT = 2 /* hit a span end */ };
+
+/* First boundary with t >= eps — the scan at reference include/path-trace.h:66-101. */
+typedef struct PtbHit {
+    float t;          /* -1 on miss                                                               */
+    float normal[3];  /* faces against the ray: startNormal, or -endNormal (path-trace.h:75,89)   */
+    int32_t kind;     /* PTB_HIT_*                                                                */
+    int32_t prim;     /* primitive whose surface was hit, -1 on miss                              */
+    int32_t material; /* its material, -1 on miss                                                 */
+    int32_t n_spans;  /* length of the root span list for this ray (may exceed max_spans)         */
+} PtbHit;
+
+/* One span of the root iterator (reference include/span.h:12-120). */
+typedef struct PtbSpan {
+    float start, end;
+    float start_normal[3];
+    float end_normal[3];
+    int32_t start_prim, end_prim;         /* primitive that contributed each boundary             */
+    int32_t start_material, end_material;
+} PtbSpan;
+
+/* flags for ptb200_intersect* and PtbRenderParams.flags */
+enum {
+    PTB_FLAG_EXACT = 1u,    /* no FMA contraction, IEEE div/sqrt: bit-identical t with the x86-64
+                               reference build.  Without it the compiler may fuse a*b+c and use
+                               rsqrt-based normalisation (|rel err| < 1e-6, within the 1e-5 gate). */
+    PTB_FLAG_BILINEAR = 2u, /* non-reference extra: bilinear image fetch instead of the reference's
+                               nearest texel                                        */
+    PTB_FLAG_REJECTION = 4u /* scatter by the reference's literal rejection loops
+                               (path-trace.h:142-158) instead of the divergence-free cap sampler   */
+};
+
+/* ---- rendering ------------------------------------------------------------------------------ */
+
+typedef struct PtbRenderParams {
+    int32_t width, height;         /* screenXResolution / screenYResolution of tracePixel          */
+    int32_t x0, y0, x1, y1;        /* pixel rectangle to render, [x0,x1) x [y0,y1); 0,0,0,0 = all  */
+    int32_t spp;                   /* camera samples per pixel rendered by THIS call               */
+    int32_t sample_offset;         /* global index of this call's first sample                     */
+    int32_t sample_stride;         /* global index step (multi-GPU: rank g renders g, g+G, ...)    */
+    int32_t max_depth;             /* rayDepth (reference src/test.cpp:36: 16)                     */
+    float screen_width, screen_height, screen_distance; /* tracePixel's screenWidth/Height/Distance */
+    uint64_t seed;
+    uint32_t flags;                /* PTB_FLAG_*                                                   */
+    int32_t samples_per_pass;      /* camera samples per pixel in flight per wavefront pass; 0=auto */
+} PtbRenderParams;
+
+typedef struct PtbStats {
+    uint64_t paths;          /* camera samples completed                                           */
+    uint64_t rays;           /* ray segments intersected against the whole scene                   */
+    uint64_t launches;       /* kernels launched by this call                                      */
+    uint64_t queue_bytes;    /* bytes read + written through the HBM ray queues                    */
+    float ms_total;          /* device time of the whole call (CUDA events on the render stream)   */
+    float ms_primary;        /* ... of the primary (raygen+intersect+shade) kernels                */
+    float ms_bounce;         /* ... of the bounce (queue -> intersect+shade -> queue) kernels      */
+    float ms_resolve;        /* ... of the framebuffer resolve kernel                              */
+    uint64_t rays_primary;   /* rays traced by the primary kernels                                 */
+    uint64_t rays_bounce;    /* rays traced by the bounce kernels                                  */
+} PtbStats;
+
+/* ---- entry points --------------------------------------------------------------------------- */
+
+const char *ptb200_last_error(void);
+int ptb200_abi_version(void);
+int ptb200_device_count(void);
+
+/* Copies everything it needs (caller keeps its buffers); the scene lives on the CUDA device that
+ * is current at the time of the call.  Validates the program (stack discipline, index ranges). */
+int ptb200_scene_create(const PtbSceneDesc *desc, PtbScene **out);
+void ptb200_scene_destroy(PtbScene *scene);
+/* Appends an image after create (texops may name images not yet uploaded at create time). */
+int ptb200_image_upload(PtbScene *scene, const float *rgba, int width, int height, int *handle);
+
+/* Host-buffer ray batch: origins/dirs are n x 3 floats.  hits: n records.  spans: optional
+ * n x max_spans records (NULL to skip).  Copies in, runs the CSG kernel, copies out. */
+int ptb200_intersect(PtbScene *scene, const float *origins, const float *dirs, size_t n,
+                     PtbHit *hits, PtbSpan *spans, int max_spans, uint32_t flags);
+/* Device-resident variant: rays as two float4 arrays (xyz + pad), results stay on the device.
+ * stream is a cudaStream_t (NULL = default stream).  Asynchronous. */
+int ptb200_intersect_device(PtbScene *scene, const void *d_origins4, const void *d_dirs4, size_t n,
+                            void *d_hits, void *d_spans, int max_spans, uint32_t flags, void *stream);
+
+/* Evaluates texture program <tex_root> at n positions (n x 3 floats, host): the reference's
+ * Texture::getColor -> rgb (n x 3) and Texture::getFloat -> f (n); either output may be NULL. */
+int ptb200_texture_eval(PtbScene *scene, int tex_root, const float *positions, size_t n,
+                        float *rgb, float *f, uint32_t flags);
+
+/* Synchronous frame render.  rgba_out: host, width*height*4 floats, mean radiance over spp in
+ * rgb and 1 in alpha (pixels outside the rectangle are left untouched). */
+int ptb200_render(PtbScene *scene, const PtbRenderParams *params, float *rgba_out, PtbStats *stats);
+/* Adds this call's UNNORMALISED radiance sums (rgb) and completed-sample counts (alpha) into a
+ * device buffer of width*height float4.  Used for sample-sharded multi-GPU rendering: every rank
+ * accumulates its slice, one NCCL sum-reduce follows, ptb200_resolve_device divides.  Synchronous
+ * with respect to <stream> only if stats != NULL. */
+int ptb200_render_accumulate_device(PtbScene *scene, const PtbRenderParams *params, void *d_accum4,
+                                    PtbStats *stats, void *stream);
+/* rgba[i] = (accum.rgb / accum.a, 1) where accum.a > 0, else 0.  In place allowed. */
+int ptb200_resolve_device(const void *d_accum4, void *d_rgba4, size_t n_pixels, void *stream);
+
+/* Progressive / asynchronous boundary mirroring BlockRenderer::done()/copyToBuffer()
+ * (reference src/test.cpp:310-323).  One job at a time per scene. */
+typedef struct PtbJob PtbJob;
+int ptb200_render_async(PtbScene *scene, const PtbRenderParams *params, PtbJob **job);
+int ptb200_job_done(PtbJob *job);                       /* 1 finished, 0 running, <0 error        */
+/* Copies the pixels that already have at least one completed sample into rgba (host,
+ * width*height*4); others are left untouched.  May be called while the job runs. */
+int ptb200_job_read(PtbJob *job, float *rgba, int width, int height);
+int ptb200_job_wait(PtbJob *job, PtbStats *stats);
+void ptb200_job_destroy(PtbJob *job);
+
+/* FP32 FMA-chain microbenchmark on the current device: measured lane-FMA/s (the FP32 issue-peak
+ * denominator of the roofline). */
+int ptb200_fp32_peak(double *fma_per_second, double *sm_clock_mhz);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTB200_H_INCLUDED */

@@ -1,0 +1,73 @@
+// ptb_scene_dev.cuh — device-side view of a flattened scene (all pointers are device memory).
+#pragma once
+#include "ptb_csg.cuh"
+
+namespace ptb
+{
+
+struct DevImage
+{
+    cudaTextureObject_t tex; // float4 2D array, point filter, border (= black outside) addressing
+    cudaTextureObject_t texLinear; // same array, bilinear (PTB_FLAG_BILINEAR extra)
+    int w, h;
+};
+
+struct DevMaterial
+{
+    int tex[5];  // PTB_MAT_* texture roots
+    float ior;   // relative ior when leaving the material (include/path-trace.h:93)
+    float iorIn; // float(1.0 / ior): relative ior when entering (include/path-trace.h:79)
+    int pad;
+};
+
+struct DevScene
+{
+    const uint4 *program;     // compiled CSG stream (see ptb_csg.cuh), programWords 16-byte words
+    int programWords;
+    const float4 *primGeo;    // [n_prims] sphere: c.xyz, r^2; plane: n.xyz, d
+    const int4 *primMeta;     // [n_prims] type, material, chain first, chain count
+    const int *chainXf;       // xform indices, outermost first
+    const float4 *xforms;     // [n_xforms][6]: rows of m, rows of inv
+    const DevMaterial *materials;
+    const int2 *texops;       // kind, arg
+    const float *texdata;
+    const DevImage *images;
+    int nPrims, nMaterials, nTexops, nImages;
+    int maxStack;             // deepest list stack the program reaches
+    int poolBound;            // worst-case pool slots (incl. merge scratch)
+};
+
+// Normal of primitive `tag>>1` at parameter t of the WORLD ray (o, d), brought back through its
+// TransformedObject chain and sign-flipped per the tag: what the reference carries in
+// Span::startNormal / endNormal (src/sphere.cpp:47-48, src/plane.cpp:29-30,
+// include/span.h:122-127 once per wrapper, include/span.h:100-113 flips).
+template <bool EX>
+__device__ __forceinline__ V3 boundaryNormal(const DevScene &sc, uint32_t tag, float t, V3 o, V3 d)
+{
+    typedef Ar<EX> A;
+    int prim = (int)(tag >> 1);
+    int4 meta = __ldg(&sc.primMeta[prim]);
+    float4 g = __ldg(&sc.primGeo[prim]);
+    V3 n;
+    if(meta.x == PTB_PRIM_SPHERE_)
+    {
+        for(int k = 0; k < meta.w; k++)
+        {
+            const float4 *x = sc.xforms + 6 * (size_t)__ldg(&sc.chainXf[meta.z + k]);
+            float4 r0 = __ldg(x), r1 = __ldg(x + 1), r2 = __ldg(x + 2);
+            o = A::apply(r0, r1, r2, o);
+            d = A::applyNoTranslate(r0, r1, r2, d);
+        }
+        n = A::normalize(A::sub(A::point(o, d, t), mk(g.x, g.y, g.z)));
+    }
+    else
+        n = A::normalize(mk(g.x, g.y, g.z));
+    for(int k = meta.w - 1; k >= 0; k--)
+    {
+        const float4 *x = sc.xforms + 6 * (size_t)__ldg(&sc.chainXf[meta.z + k]) + 3;
+        n = A::normalize(A::applyNoTranslate(__ldg(x), __ldg(x + 1), __ldg(x + 2), n));
+    }
+    return (tag & 1u) ? neg(n) : n;
+}
+
+} // namespace ptb
