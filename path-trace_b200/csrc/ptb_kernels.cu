@@ -1,0 +1,389 @@
+// ptb_kernels.cu — the sm_100a kernels of the render path.
+//
+//   intersectKernel   ray batch -> CSG span lists -> first hit          (BASELINE config 3)
+//   primaryKernel     raygen + intersect + shade, survivors -> HBM queue (wavefront stage 0)
+//   bounceKernel      HBM queue -> intersect + shade -> HBM queue        (wavefront stage k)
+//   resolveKernel     accumulation buffer -> mean radiance
+//
+// Work is branchy scalar FP32 (no tensor cores, no RT cores on B200).  Grids are persistent:
+// a multiple of the SM count, each warp striding over the work; the CSG program is staged
+// into shared memory once per CTA and read warp-uniformly; span lists sit in a bank-conflict
+// free [slot][thread] shared-memory pool; queue records are four float4 SoA streams written
+// through __ballot_sync/__popc warp-aggregated compaction so every store is coalesced.
+#include "ptb_launch.h"
+#include "ptb_shade.cuh"
+
+namespace ptb
+{
+
+// ---- shared memory carve-up -----------------------------------------------------------------
+size_t csgSharedBytes(const DevScene &sc, int threads, int cap, bool stageProgram)
+{
+    size_t bytes = stageProgram ? (size_t)sc.programWords * 16 : 0;
+    bytes += (size_t)cap * threads * 12;                 // t0, t1, tags
+    bytes += (size_t)sc.maxStack * threads * 2;          // stack-entry start offsets (u16)
+    return (bytes + 15) & ~(size_t)15;
+}
+
+struct CsgShared
+{
+    const uint4 *program;
+    Pool pool;
+};
+
+__device__ __forceinline__ CsgShared setupCsg(const DevScene &sc, int cap, int stageProgram, float *overflow, size_t ovfStride)
+{
+    extern __shared__ uint4 smem[];
+    CsgShared s;
+    uint4 *p = smem;
+    if(stageProgram)
+    {
+        for(int i = threadIdx.x; i < sc.programWords; i += blockDim.x)
+            p[i] = sc.program[i];
+        s.program = p;
+        p += sc.programWords;
+    }
+    else
+        s.program = sc.program;
+    float *f = reinterpret_cast<float *>(p);
+    int T = blockDim.x;
+    s.pool.s0 = f + threadIdx.x;
+    s.pool.s1 = f + (size_t)cap * T + threadIdx.x;
+    s.pool.sg = reinterpret_cast<uint32_t *>(f + 2 * (size_t)cap * T) + threadIdx.x;
+    s.pool.starts = reinterpret_cast<uint16_t *>(f + 3 * (size_t)cap * T) + threadIdx.x;
+    s.pool.stride = T;
+    s.pool.cap = cap;
+    s.pool.ovf = overflow ? overflow + (size_t)blockIdx.x * T + threadIdx.x : nullptr;
+    s.pool.ovfStride = ovfStride;
+    __syncthreads();
+    return s;
+}
+
+// Intersects one ray with the scene and resolves the first hit (normal, material, relative ior).
+template <bool EX>
+__device__ __forceinline__ int traceFirstHit(const DevScene &sc, const CsgShared &cs, V3 o, V3 d, Hit &hit, uint32_t &tag, int &nSpans)
+{
+    nSpans = evalProgram<EX>(cs.program, cs.pool, o, d);
+    float t = -1.f;
+    tag = 0u;
+    int kind = firstHit(cs.pool, nSpans, t, tag);
+    hit.t = t;
+    if(kind == PTB_HIT_MISS)
+        return kind;
+    V3 n = boundaryNormal<EX>(sc, tag, t, o, d);
+    int mat = __ldg(&sc.primMeta[tag >> 1]).y;
+    hit.mat = mat;
+    if(kind == PTB_HIT_ENTER)
+    { // path-trace.h:72-81
+        hit.n = n;
+        hit.ior = sc.materials[mat].iorIn;
+    }
+    else
+    { // path-trace.h:86-95
+        hit.n = neg(n);
+        hit.ior = sc.materials[mat].ior;
+    }
+    return kind;
+}
+
+// ---- ray-batch intersection -------------------------------------------------------------------
+template <bool EX>
+__global__ void __launch_bounds__(128) intersectKernel(DevScene sc, int cap, int stageProgram, float *overflow, size_t ovfStride, const float4 *__restrict__ origins,
+                                                       const float4 *__restrict__ dirs, size_t n, PtbHit *__restrict__ hits, PtbSpan *__restrict__ spans,
+                                                       int maxSpans)
+{
+    CsgShared cs = setupCsg(sc, cap, stageProgram, overflow, ovfStride);
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for(size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        float4 o4 = __ldg(&origins[i]), d4 = __ldg(&dirs[i]);
+        V3 o = mk(o4.x, o4.y, o4.z), d = mk(d4.x, d4.y, d4.z);
+        Hit hit;
+        uint32_t tag;
+        int nSpans;
+        int kind = traceFirstHit<EX>(sc, cs, o, d, hit, tag, nSpans);
+        PtbHit out;
+        out.t = hit.t;
+        out.kind = kind;
+        out.n_spans = nSpans;
+        if(kind == PTB_HIT_MISS)
+        {
+            out.normal[0] = out.normal[1] = out.normal[2] = 0.f;
+            out.prim = out.material = -1;
+        }
+        else
+        {
+            out.normal[0] = hit.n.x, out.normal[1] = hit.n.y, out.normal[2] = hit.n.z;
+            out.prim = (int)(tag >> 1);
+            out.material = hit.mat;
+        }
+        // 32-byte record as two float4 stores
+        float4 *dst = reinterpret_cast<float4 *>(hits + i);
+        dst[0] = make_float4(out.t, out.normal[0], out.normal[1], out.normal[2]);
+        dst[1] = make_float4(__int_as_float(out.kind), __int_as_float(out.prim), __int_as_float(out.material), __int_as_float(out.n_spans));
+        if(spans)
+        {
+            int m = nSpans < maxSpans ? nSpans : maxSpans;
+            for(int s = 0; s < m; s++)
+            {
+                SpanRec r = cs.pool.load(s);
+                PtbSpan &ps = spans[i * (size_t)maxSpans + s];
+                V3 sn = boundaryNormal<EX>(sc, startTag(r), r.t0, o, d);
+                V3 en = boundaryNormal<EX>(sc, endTag(r), r.t1, o, d);
+                ps.start = r.t0, ps.end = r.t1;
+                ps.start_normal[0] = sn.x, ps.start_normal[1] = sn.y, ps.start_normal[2] = sn.z;
+                ps.end_normal[0] = en.x, ps.end_normal[1] = en.y, ps.end_normal[2] = en.z;
+                ps.start_prim = (int)(startTag(r) >> 1), ps.end_prim = (int)(endTag(r) >> 1);
+                ps.start_material = __ldg(&sc.primMeta[ps.start_prim]).y;
+                ps.end_material = __ldg(&sc.primMeta[ps.end_prim]).y;
+            }
+        }
+    }
+}
+
+void launchIntersect(const DevScene &sc, const CsgConfig &cfg, const float4 *origins, const float4 *dirs, size_t n, PtbHit *hits, PtbSpan *spans, int maxSpans,
+                     bool exact, cudaStream_t stream)
+{
+    if(exact)
+    {
+        cudaFuncSetAttribute(intersectKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        intersectKernel<true><<<cfg.blocks, cfg.threads, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.stageProgram, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans,
+                                                                                  maxSpans);
+    }
+    else
+    {
+        cudaFuncSetAttribute(intersectKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        intersectKernel<false><<<cfg.blocks, cfg.threads, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.stageProgram, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans,
+                                                                                   maxSpans);
+    }
+}
+
+// ---- wavefront render stages --------------------------------------------------------------------
+// Queue record (64 B, four coalesced float4 streams):
+//   q0 = origin.xyz, pixel        q1 = dir.xyz, strength
+//   q2 = throughput.rgb, sample   q3 = depth, rng block, -, -
+__device__ __forceinline__ void queueStore(const RayQueue &q, unsigned idx, const PathState &ps)
+{
+    q.q0[idx] = make_float4(ps.o.x, ps.o.y, ps.o.z, __uint_as_float(ps.pixel));
+    q.q1[idx] = make_float4(ps.d.x, ps.d.y, ps.d.z, ps.strength);
+    q.q2[idx] = make_float4(ps.thr.x, ps.thr.y, ps.thr.z, __uint_as_float(ps.sample));
+    q.q3[idx] = make_float4(__uint_as_float(ps.depth), __uint_as_float(ps.rngBlock), 0.f, 0.f);
+}
+__device__ __forceinline__ void queueLoad(const RayQueue &q, unsigned idx, PathState &ps)
+{
+    float4 a = __ldcs(&q.q0[idx]), b = __ldcs(&q.q1[idx]), c = __ldcs(&q.q2[idx]), e = __ldcs(&q.q3[idx]);
+    ps.o = mk(a.x, a.y, a.z), ps.pixel = __float_as_uint(a.w);
+    ps.d = mk(b.x, b.y, b.z), ps.strength = b.w;
+    ps.thr = mk(c.x, c.y, c.z), ps.sample = __float_as_uint(c.w);
+    ps.depth = __float_as_uint(e.x), ps.rngBlock = __float_as_uint(e.y);
+}
+
+// Framebuffer accumulation: one 16-byte vector reduction per contribution.  rgb = radiance sum,
+// a = completed camera samples (so a progressive reader can divide at any time).
+__device__ __forceinline__ void accumulate(float4 *accum, uint32_t pixel, V3 rad, float done)
+{
+    if(rad.x != 0.f || rad.y != 0.f || rad.z != 0.f || done != 0.f)
+        atomicAdd(&accum[pixel], make_float4(rad.x, rad.y, rad.z, done));
+}
+
+// One wavefront step for the path in `ps` (valid lanes only): intersect, shade, accumulate;
+// then the warp compacts its surviving lanes into the out queue.
+__device__ __forceinline__ void traceShadeEnqueue(const DevScene &sc, const CsgShared &cs, bool valid, PathState &ps, uint64_t seed, uint32_t flags, float4 *accum,
+                                                  const RayQueue &out, unsigned *outCount)
+{
+    bool alive = false;
+    if(valid)
+    {
+        Hit hit;
+        uint32_t tag;
+        int nSpans;
+        int kind = traceFirstHit<false>(sc, cs, ps.o, ps.d, hit, tag, nSpans);
+        V3 rad = mk(0.f, 0.f, 0.f);
+        if(kind != PTB_HIT_MISS)
+        {
+            Philox rng;
+            rngInit(rng, seed, ps.pixel, ps.sample, ps.rngBlock);
+            alive = shadeVertex(sc, ps, hit, rng, flags, rad);
+            ps.rngBlock = rng.block;
+        }
+        accumulate(accum, ps.pixel, rad, alive ? 0.f : 1.f);
+    }
+    unsigned mask = __ballot_sync(0xFFFFFFFFu, alive);
+    if(mask)
+    {
+        unsigned lane = threadIdx.x & 31u;
+        int leader = __ffs(mask) - 1;
+        unsigned base = 0;
+        if((int)lane == leader)
+            base = atomicAdd(outCount, (unsigned)__popc(mask));
+        base = __shfl_sync(0xFFFFFFFFu, base, leader);
+        if(alive)
+            queueStore(out, base + __popc(mask & ((1u << lane) - 1u)), ps);
+    }
+}
+
+__global__ void __launch_bounds__(128) primaryKernel(DevScene sc, int cap, int stageProgram, float *overflow, size_t ovfStride, RenderPass pass, float4 *accum,
+                                                     RayQueue out, unsigned *outCount)
+{
+    CsgShared cs = setupCsg(sc, cap, stageProgram, overflow, ovfStride);
+    const unsigned nPix = (unsigned)pass.rw * (unsigned)pass.rh;
+    const unsigned long long total = (unsigned long long)nPix * (unsigned)pass.samplesThisPass;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    // warp-uniform trip count: every lane of a warp iterates together so the ballot is full
+    unsigned long long first = (unsigned long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31u);
+    for(unsigned long long base = first; base < total; base += stride)
+    {
+        unsigned long long i = base + (threadIdx.x & 31u);
+        bool valid = i < total;
+        PathState ps;
+        if(valid)
+        {
+            unsigned s = (unsigned)(i / nPix), p = (unsigned)(i % nPix);
+            int px = pass.x0 + (int)(p % (unsigned)pass.rw), py = pass.y0 + (int)(p / (unsigned)pass.rw);
+            ps.pixel = (unsigned)py * (unsigned)pass.width + (unsigned)px;
+            ps.sample = (unsigned)(pass.sampleBase + (int)s * pass.sampleStride);
+            Philox rng;
+            rngInit(rng, pass.seed, ps.pixel, ps.sample, 0u);
+            uint4 u = rngNext4(rng);
+            ps.rngBlock = rng.block;
+            // tracePixel with per-sample jitter, reference include/path-trace.h:191-196
+            float x = 2.f * ((float)px + u01(u.x)) / (float)pass.width - 1.f;
+            float y = 1.f - 2.f * ((float)py + u01(u.y)) / (float)pass.height;
+            ps.o = mk(0.f, 0.f, 0.f);
+            ps.d = mk(x * pass.sw, y * pass.sh, -pass.sd);
+            ps.thr = mk(1.f, 1.f, 1.f);
+            ps.strength = 1.f;
+            ps.depth = (unsigned)pass.maxDepth;
+        }
+        traceShadeEnqueue(sc, cs, valid, ps, pass.seed, pass.flags, accum, out, outCount);
+    }
+}
+
+__global__ void __launch_bounds__(128) bounceKernel(DevScene sc, int cap, int stageProgram, float *overflow, size_t ovfStride, RenderPass pass, float4 *accum,
+                                                    RayQueue in, const unsigned *__restrict__ inCount, RayQueue out, unsigned *outCount)
+{
+    const unsigned total = *inCount;
+    if(total == 0u)
+        return;
+    CsgShared cs = setupCsg(sc, cap, stageProgram, overflow, ovfStride);
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    unsigned long long first = (unsigned long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31u);
+    for(unsigned long long base = first; base < total; base += stride)
+    {
+        unsigned long long i = base + (threadIdx.x & 31u);
+        bool valid = i < total;
+        PathState ps;
+        if(valid)
+            queueLoad(in, (unsigned)i, ps);
+        traceShadeEnqueue(sc, cs, valid, ps, pass.seed, pass.flags, accum, out, outCount);
+    }
+}
+
+void launchPrimary(const DevScene &sc, const CsgConfig &cfg, const RenderPass &pass, float4 *accum, RayQueue out, unsigned *outCount, cudaStream_t stream)
+{
+    cudaFuncSetAttribute(primaryKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+    primaryKernel<<<cfg.blocks, cfg.threads, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.stageProgram, cfg.overflow, cfg.ovfStride, pass, accum, out, outCount);
+}
+void launchBounce(const DevScene &sc, const CsgConfig &cfg, const RenderPass &pass, float4 *accum, RayQueue in, const unsigned *inCount, RayQueue out,
+                  unsigned *outCount, cudaStream_t stream)
+{
+    cudaFuncSetAttribute(bounceKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+    bounceKernel<<<cfg.blocks, cfg.threads, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.stageProgram, cfg.overflow, cfg.ovfStride, pass, accum, in, inCount, out, outCount);
+}
+
+// ---- resolve ------------------------------------------------------------------------------------
+__global__ void resolveKernel(const float4 *__restrict__ accum, float4 *__restrict__ rgba, size_t n)
+{
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for(size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        float4 a = accum[i];
+        float inv = a.w > 0.f ? 1.f / a.w : 0.f;
+        rgba[i] = make_float4(a.x * inv, a.y * inv, a.z * inv, a.w > 0.f ? 1.f : 0.f);
+    }
+}
+void launchResolve(const float4 *accum, float4 *rgba, size_t nPixels, cudaStream_t stream)
+{
+    int blocks = (int)((nPixels + 255) / 256);
+    if(blocks > 148 * 8)
+        blocks = 148 * 8;
+    if(blocks < 1)
+        blocks = 1;
+    resolveKernel<<<blocks, 256, 0, stream>>>(accum, rgba, nPixels);
+}
+
+// ---- inspection kernels (known-answer tests through the C ABI) ----------------------------------
+__global__ void textureEvalKernel(DevScene sc, int root, const float *__restrict__ pos, size_t n, float *__restrict__ rgb, float *__restrict__ f, uint32_t flags)
+{
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for(size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        V3 p = mk(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]);
+        V3 c;
+        float v;
+        evalTexture(sc, root, p, false, flags & PTB_FLAG_BILINEAR, c, v);
+        if(rgb)
+            rgb[3 * i] = c.x, rgb[3 * i + 1] = c.y, rgb[3 * i + 2] = c.z;
+        if(f)
+            f[i] = v;
+    }
+}
+void launchTextureEval(const DevScene &sc, int root, const float *pos, size_t n, float *rgb, float *f, uint32_t flags, cudaStream_t stream)
+{
+    int blocks = (int)((n + 127) / 128);
+    blocks = blocks < 1 ? 1 : (blocks > 1184 ? 1184 : blocks);
+    textureEvalKernel<<<blocks, 128, 0, stream>>>(sc, root, pos, n, rgb, f, flags);
+}
+
+// Draws n scatter directions for one (normal, mirror vector, scatter coefficient) so the lobe
+// sampler can be checked statistically against the reference's rejection loops.  A direction
+// of (0,0,0) marks a dropped vertex (the 1000-try give-up).
+__global__ void scatterSampleKernel(V3 normal, V3 refl, float scatter, size_t n, uint64_t seed, uint32_t flags, float *__restrict__ dirs)
+{
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for(size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        Philox rng;
+        rngInit(rng, seed, (uint32_t)i, (uint32_t)(i >> 32), 0u);
+        V3 d = mk(0.f, 0.f, 0.f);
+        bool ok = (flags & PTB_FLAG_REJECTION) ? scatterRejection(rng, normal, refl, scatter, d) : scatterCap(rng, normal, refl, scatter, d);
+        if(!ok)
+            d = mk(0.f, 0.f, 0.f);
+        dirs[3 * i] = d.x, dirs[3 * i + 1] = d.y, dirs[3 * i + 2] = d.z;
+    }
+}
+void launchScatterSample(const float *normal, const float *refl, float scatter, size_t n, uint64_t seed, uint32_t flags, float *dirs, cudaStream_t stream)
+{
+    int blocks = (int)((n + 127) / 128);
+    blocks = blocks < 1 ? 1 : (blocks > 1184 ? 1184 : blocks);
+    scatterSampleKernel<<<blocks, 128, 0, stream>>>(mk(normal[0], normal[1], normal[2]), mk(refl[0], refl[1], refl[2]), scatter, n, seed, flags, dirs);
+}
+
+// ---- FP32 issue-peak microbenchmark (roofline denominator) -----------------------
+// Eight independent FFMA chains per thread: enough ILP to saturate both FP32 datapaths.
+__global__ void __launch_bounds__(256) fmaPeakKernel(float *out, int iters, float a, float b)
+{
+    float x0 = threadIdx.x, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f, x6 = x0 + 6.f, x7 = x0 + 7.f;
+    for(int i = 0; i < iters; i++)
+    {
+#pragma unroll
+        for(int k = 0; k < 16; k++)
+        {
+            x0 = fmaf(x0, a, b), x1 = fmaf(x1, a, b), x2 = fmaf(x2, a, b), x3 = fmaf(x3, a, b);
+            x4 = fmaf(x4, a, b), x5 = fmaf(x5, a, b), x6 = fmaf(x6, a, b), x7 = fmaf(x7, a, b);
+        }
+    }
+    float s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+    if(s == 12345.678f)
+        out[0] = s;
+}
+double launchFmaPeak(int blocks, int threads, int iters, cudaStream_t stream)
+{
+    static float *sink = nullptr;
+    if(!sink)
+        cudaMalloc(&sink, sizeof(float));
+    fmaPeakKernel<<<blocks, threads, 0, stream>>>(sink, iters, 0.999f, 0.001f);
+    return (double)blocks * threads * (double)iters * 16.0 * 8.0;
+}
+
+} // namespace ptb

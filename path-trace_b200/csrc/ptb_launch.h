@@ -1,0 +1,58 @@
+// ptb_launch.h — internal interface between the C-ABI host code (ptb_capi.cu) and the kernels
+// (ptb_kernels.cu).  Not part of the public boundary.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "ptb_scene_dev.cuh"
+
+namespace ptb
+{
+
+// How one kernel launch lays out its shared memory and span-pool overflow.
+struct CsgConfig
+{
+    int threads;       // threads per block
+    int blocks;        // grid size (persistent: a multiple of the SM count)
+    int cap;           // span-pool slots per thread kept in shared memory
+    int stageProgram;  // 1: copy the program stream into shared memory first
+    size_t smemBytes;  // dynamic shared memory per block
+    float *overflow;   // global spill area or NULL when cap >= scene.poolBound
+    size_t ovfStride;  // = blocks * threads
+};
+
+// Ray queue: four float4 SoA streams (64 B per ray), see ptb_kernels.cu.
+struct RayQueue
+{
+    float4 *q0, *q1, *q2, *q3;
+};
+
+struct RenderPass
+{
+    int width, height;          // full image
+    int x0, y0, rw, rh;         // rectangle rendered
+    int samplesThisPass;        // camera samples per pixel in this pass
+    int sampleBase;             // global index of this pass's first sample
+    int sampleStride;
+    int maxDepth;
+    float sw, sh, sd;
+    uint64_t seed;
+    uint32_t flags;
+};
+
+void launchIntersect(const DevScene &sc, const CsgConfig &cfg, const float4 *origins, const float4 *dirs, size_t n, PtbHit *hits, PtbSpan *spans, int maxSpans,
+                     bool exact, cudaStream_t stream);
+// Primary wavefront stage: raygen + intersect + shade for rw*rh*samplesThisPass camera samples;
+// survivors are appended to `out`, *outCount counts them.
+void launchPrimary(const DevScene &sc, const CsgConfig &cfg, const RenderPass &pass, float4 *accum, RayQueue out, unsigned *outCount, cudaStream_t stream);
+// Bounce stage: *inCount rays from `in` -> intersect + shade -> survivors appended to `out`.
+void launchBounce(const DevScene &sc, const CsgConfig &cfg, const RenderPass &pass, float4 *accum, RayQueue in, const unsigned *inCount, RayQueue out,
+                  unsigned *outCount, cudaStream_t stream);
+void launchResolve(const float4 *accum, float4 *rgba, size_t nPixels, cudaStream_t stream);
+void launchTextureEval(const DevScene &sc, int root, const float *pos, size_t n, float *rgb, float *f, uint32_t flags, cudaStream_t stream);
+void launchScatterSample(const float *normal, const float *refl, float scatter, size_t n, uint64_t seed, uint32_t flags, float *dirs, cudaStream_t stream);
+// FMA-chain microbenchmark: returns lane-FMAs executed.
+double launchFmaPeak(int blocks, int threads, int iters, cudaStream_t stream);
+size_t csgSharedBytes(const DevScene &sc, int threads, int cap, bool stageProgram);
+
+} // namespace ptb

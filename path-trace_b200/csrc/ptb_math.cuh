@@ -22,7 +22,7 @@ struct V3
 {
     float x, y, z;
 };
-__device__ __forceinline__ V3 mk(float x, float y, float z)
+__host__ __device__ __forceinline__ V3 mk(float x, float y, float z)
 {
     V3 v;
     v.x = x, v.y = y, v.z = z;

@@ -1,5 +1,6 @@
 // ptb_scene_dev.cuh — device-side view of a flattened scene (all pointers are device memory).
 #pragma once
+#include "ptb200.h"
 #include "ptb_csg.cuh"
 
 namespace ptb
@@ -49,7 +50,7 @@ __device__ __forceinline__ V3 boundaryNormal(const DevScene &sc, uint32_t tag, f
     int4 meta = __ldg(&sc.primMeta[prim]);
     float4 g = __ldg(&sc.primGeo[prim]);
     V3 n;
-    if(meta.x == PTB_PRIM_SPHERE_)
+    if(meta.x == PTB_PRIM_SPHERE)
     {
         for(int k = 0; k < meta.w; k++)
         {

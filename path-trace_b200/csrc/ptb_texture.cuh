@@ -1,0 +1,193 @@
+// ptb_texture.cuh — texture-program interpreter.
+//
+// A texture is a linear chain of wrapper ops ending in one leaf (include/ptb200.h).  Position
+// wrappers act on the way down, colour filters on the way back up.  Image fetches go through
+// texture objects on float4 CUDA arrays with POINT filtering (the reference is nearest-texel,
+// SURVEY.md Q8) and border addressing (black outside, as Image::getPixel,
+// reference src/image.cpp:366-380).
+#pragma once
+#include "ptb_scene_dev.cuh"
+
+namespace ptb
+{
+
+// ImageTexture::getColor addressing, reference include/image_texture.h:18-28
+__device__ __forceinline__ float4 imageLookup(const DevImage &im, V3 v, bool bilinear)
+{
+    float x = v.x - floorf(v.x);
+    float y = v.y - floorf(v.y);
+    y = 1.0f - y;
+    x *= (float)im.w;
+    y *= (float)im.h;
+    if(bilinear)
+        return tex2D<float4>(im.texLinear, x, y);
+    return tex2D<float4>(im.tex, floorf(x) + 0.5f, floorf(y) + 0.5f);
+}
+// ImageSkyboxTexture::getColor(x, y, image), reference include/image_texture.h:77-85 (the
+// reference evaluates x*0.5+0.5 in double and narrows; done the same way here)
+__device__ __forceinline__ float4 faceLookup(const DevImage &im, float x, float y, bool bilinear)
+{
+    x = (float)((double)x * 0.5 + 0.5);
+    y = (float)(0.5 - (double)y * 0.5);
+    x *= (float)im.w;
+    y *= (float)im.h;
+    if(bilinear)
+        return tex2D<float4>(im.texLinear, x, y);
+    return tex2D<float4>(im.tex, floorf(x) + 0.5f, floorf(y) + 0.5f);
+}
+// cube face by dominant axis with the reference's strict '>' tie rules,
+// include/image_texture.h:91-110.  Faces: top, bottom, left, right, front, back.
+__device__ __forceinline__ float4 skyboxLookup(const DevImage *im, V3 v, bool bilinear)
+{
+    if(isZero(v))
+        return make_float4(0.f, 0.f, 0.f, 0.f);
+    float ax = fabsf(v.x), ay = fabsf(v.y), az = fabsf(v.z);
+    if(ax > ay && ax > az)
+    {
+        if(v.x < 0.f)
+            return faceLookup(im[2], __fdiv_rn(-v.z, ax), __fdiv_rn(v.y, ax), bilinear);
+        return faceLookup(im[3], __fdiv_rn(v.z, ax), __fdiv_rn(v.y, ax), bilinear);
+    }
+    if(ay > az)
+    {
+        if(v.y < 0.f)
+            return faceLookup(im[1], __fdiv_rn(-v.x, ay), __fdiv_rn(v.z, ay), bilinear);
+        return faceLookup(im[0], __fdiv_rn(v.x, ay), __fdiv_rn(v.z, ay), bilinear);
+    }
+    if(v.z < 0.f)
+        return faceLookup(im[5], __fdiv_rn(v.x, az), __fdiv_rn(v.y, az), bilinear);
+    return faceLookup(im[4], __fdiv_rn(-v.x, az), __fdiv_rn(v.y, az), bilinear);
+}
+// LogTexture::myLog, reference include/filter_texture.h:61-66
+__device__ __forceinline__ float texLog(float v)
+{
+    if(v <= 1e-30f)
+        return 0.f;
+    return 0.5f + logf(v) / 0.693147180559945f / 256.f;
+}
+// Texture::getFloat default, reference include/texture.h:14-18
+__device__ __forceinline__ float meanRgb(V3 c) { return (c.x + c.y + c.z) * (1.0f / 3.0f); }
+
+// Position wrappers use exact IEEE arithmetic (they are a few ops per shaded hit and decide
+// which texel a point sample lands on).
+__device__ __forceinline__ V3 texMirrorBall(V3 p) // include/transform_texture.h:46-59
+{
+    if(isZero(p))
+        return p;
+    V3 v = Ar<true>::normalize(p);
+    if(v.z <= -1.f)
+        return mk(0.f, 0.5f, 0.f);
+    float d = __fsqrt_rn(__fadd_rn(2.f, __fmul_rn(2.f, v.z)));
+    if(d == 0.f)
+        return mk(0.f, 0.5f, 0.f);
+    float xt = __fdiv_rn(v.x, d), yt = __fdiv_rn(v.y, d);
+    return mk((float)((double)xt * 0.5 + 0.5), (float)((double)yt * 0.5 + 0.5), 0.f);
+}
+__device__ __forceinline__ V3 texSpherical(V3 p) // include/transform_texture.h:73-85
+{
+    if(isZero(p))
+        return p;
+    const double PI = 3.14159265358979323846;
+    V3 v = Ar<true>::normalize(p);
+    float theta = atan2f(v.y, v.x);
+    if((double)theta < -PI)
+        theta = (float)((double)theta + 2 * PI);
+    if((double)theta > PI)
+        theta = (float)((double)theta - 2 * PI);
+    float phi = asinf(v.z);
+    return mk((float)((double)theta * 0.5 / PI + 0.5), (float)((double)phi / (PI / 2) * 0.5 + 0.5), 0.f);
+}
+
+// Evaluates texture chain `root` at pos.  wantFloat selects Texture::getFloat semantics:
+// position wrappers forward getFloat (texture.h:78-81, transform_texture.h:30-33), filters do
+// not override it, so under a filter the chain runs as getColor and the mean is taken above.
+__device__ __forceinline__ void evalTexture(const DevScene &sc, int root, V3 pos, bool wantFloat, bool bilinear, V3 &color, float &f)
+{
+    int i = root;
+    int2 op = __ldg(&sc.texops[i]);
+    // fast path: a bare ColorTexture (every material slot of the default materials)
+    if(op.x == PTB_TEX_CONST)
+    {
+        const float *d = sc.texdata + op.y;
+        color = mk(__ldg(d), __ldg(d + 1), __ldg(d + 2));
+        f = meanRgb(color);
+        return;
+    }
+    bool filtered = false;
+    while(!PTB_TEX_IS_LEAF(op.x))
+    {
+        if(op.x == PTB_TEX_AFFINE) // TransformedTexture, include/texture.h:74-81
+        {
+            const float *m = sc.texdata + op.y;
+            float4 r0 = make_float4(__ldg(m), __ldg(m + 1), __ldg(m + 2), __ldg(m + 3));
+            float4 r1 = make_float4(__ldg(m + 4), __ldg(m + 5), __ldg(m + 6), __ldg(m + 7));
+            float4 r2 = make_float4(__ldg(m + 8), __ldg(m + 9), __ldg(m + 10), __ldg(m + 11));
+            pos = Ar<true>::apply(r0, r1, r2, pos);
+        }
+        else if(op.x == PTB_TEX_MIRRORBALL)
+            pos = texMirrorBall(pos);
+        else if(op.x == PTB_TEX_SPHERICAL)
+            pos = texSpherical(pos);
+        else
+            filtered = true;
+        op = __ldg(&sc.texops[++i]);
+    }
+    float4 px;
+    bool alpha = false;
+    if(op.x == PTB_TEX_CONST)
+    {
+        const float *d = sc.texdata + op.y;
+        px = make_float4(__ldg(d), __ldg(d + 1), __ldg(d + 2), 0.f);
+    }
+    else if(op.x == PTB_TEX_IMAGE || op.x == PTB_TEX_IMAGE_ALPHA)
+    {
+        px = imageLookup(sc.images[op.y], pos, bilinear);
+        alpha = op.x == PTB_TEX_IMAGE_ALPHA;
+    }
+    else
+    {
+        px = skyboxLookup(sc.images + op.y, pos, bilinear);
+        alpha = op.x == PTB_TEX_SKYBOX_ALPHA;
+    }
+    if(alpha) // getColor = Color(alpha), getFloat = alpha (include/image_texture.h:45-66,135-176)
+    {
+        color = mk(px.w, px.w, px.w);
+        f = px.w;
+    }
+    else
+    {
+        color = mk(px.x, px.y, px.z);
+        f = meanRgb(color);
+    }
+    if(!filtered)
+        return;
+    for(int k = i - 1; k >= root; k--)
+    {
+        int2 w = __ldg(&sc.texops[k]);
+        if(w.x == PTB_TEX_MULTIPLY) // include/filter_texture.h:43-46
+        {
+            const float *d = sc.texdata + w.y;
+            color = mk(color.x * __ldg(d), color.y * __ldg(d + 1), color.z * __ldg(d + 2));
+        }
+        else if(w.x == PTB_TEX_LOG) // include/filter_texture.h:68-71
+            color = mk(texLog(color.x), texLog(color.y), texLog(color.z));
+    }
+    f = meanRgb(color);
+}
+
+__device__ __forceinline__ V3 texColor(const DevScene &sc, int root, V3 pos, bool bilinear)
+{
+    V3 c;
+    float f;
+    evalTexture(sc, root, pos, false, bilinear, c, f);
+    return c;
+}
+__device__ __forceinline__ float texFloat(const DevScene &sc, int root, V3 pos, bool bilinear)
+{
+    V3 c;
+    float f;
+    evalTexture(sc, root, pos, true, bilinear, c, f);
+    return f;
+}
+
+} // namespace ptb
