@@ -243,6 +243,11 @@ int ptb200_job_read(PtbJob *job, float *rgba, int width, int height);
 int ptb200_job_wait(PtbJob *job, PtbStats *stats);
 void ptb200_job_destroy(PtbJob *job);
 
+/* Draws n scatter directions (n x 3 floats, host) from the lobe sampler of the shading kernel for
+ * one unit normal, un-normalised mirror vector and scatter coefficient (reference
+ * include/path-trace.h:140-158); (0,0,0) marks a dropped vertex.  For statistical checks. */
+int ptb200_sample_scatter(const float *normal, const float *mirror, float scatter, size_t n, uint64_t seed, uint32_t flags, float *dirs);
+
 /* FP32 FMA-chain microbenchmark on the current device: measured lane-FMA/s (the FP32 issue-peak
  * denominator of the roofline). */
 int ptb200_fp32_peak(double *fma_per_second, double *sm_clock_mhz);

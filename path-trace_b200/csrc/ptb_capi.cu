@@ -1,0 +1,912 @@
+// ptb_capi.cu — implementation of the C ABI in include/ptb200.h: scene compilation and upload,
+// launch configuration, the wavefront driver.  Host C++; every entry point catches everything
+// and returns a status code (nothing throws across the boundary).
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "ptb_launch.h"
+
+using namespace ptb;
+
+namespace
+{
+thread_local std::string g_error;
+int fail(int code, const std::string &msg)
+{
+    g_error = msg;
+    return code;
+}
+#define CU(call)                                                                                           \
+    do                                                                                                     \
+    {                                                                                                      \
+        cudaError_t e_ = (call);                                                                           \
+        if(e_ != cudaSuccess)                                                                              \
+            return fail(PTB_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_));                    \
+    } while(0)
+
+struct DeviceBuffer
+{
+    void *p = nullptr;
+    size_t bytes = 0;
+    ~DeviceBuffer() { release(); }
+    void release()
+    {
+        if(p)
+            cudaFree(p);
+        p = nullptr, bytes = 0;
+    }
+    cudaError_t ensure(size_t n)
+    {
+        if(n <= bytes)
+            return cudaSuccess;
+        release();
+        cudaError_t e = cudaMalloc(&p, n);
+        if(e == cudaSuccess)
+            bytes = n;
+        return e;
+    }
+};
+
+struct ImageSlot
+{
+    cudaArray_t array = nullptr;
+    cudaTextureObject_t point = 0, linear = 0;
+    int w = 0, h = 0;
+};
+
+// Per-scene scratch for rendering (queues, counters, events); guarded by `busy`.
+struct RenderScratch
+{
+    DeviceBuffer queues, counters, overflow, accum;
+    unsigned *hostCounters = nullptr; // pinned
+    size_t hostCountersLen = 0;
+    std::vector<cudaEvent_t> events;
+    ~RenderScratch()
+    {
+        if(hostCounters)
+            cudaFreeHost(hostCounters);
+        for(cudaEvent_t e : events)
+            cudaEventDestroy(e);
+    }
+};
+} // namespace
+
+struct PtbScene
+{
+    int device = 0;
+    int smCount = 148;
+    size_t smemOptin = 0;
+    DevScene dev;
+    std::vector<void *> allocs;
+    std::vector<ImageSlot> images;
+    DevImage *dImages = nullptr;
+    int imageCapacity = 0;
+    std::mutex lock; // one render / intersect call at a time per scene
+    RenderScratch scratch;
+    bool asyncBusy = false;
+};
+
+struct PtbJob
+{
+    PtbScene *scene = nullptr;
+    PtbRenderParams params;
+    std::thread worker;
+    volatile int done = 0;
+    int status = 0;
+    std::string error;
+    PtbStats stats;
+    cudaStream_t readStream = nullptr;
+    float4 *accum = nullptr; // device, owned by the job
+    std::vector<float> staging;
+};
+
+namespace
+{
+template <typename T>
+int upload(PtbScene *s, const std::vector<T> &host, const T **out)
+{
+    *out = nullptr;
+    size_t bytes = std::max<size_t>(host.size(), 1) * sizeof(T);
+    void *p = nullptr;
+    CU(cudaMalloc(&p, bytes));
+    s->allocs.push_back(p);
+    if(!host.empty())
+        CU(cudaMemcpy(p, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice));
+    *out = (const T *)p;
+    return PTB_OK;
+}
+
+int createImage(const float *rgba, int w, int h, ImageSlot &slot)
+{
+    if(!rgba || w <= 0 || h <= 0)
+        return fail(PTB_EINVAL, "image with no pixels");
+    cudaChannelFormatDesc fmt = cudaCreateChannelDesc<float4>();
+    CU(cudaMallocArray(&slot.array, &fmt, (size_t)w, (size_t)h));
+    CU(cudaMemcpy2DToArray(slot.array, 0, 0, rgba, (size_t)w * 16, (size_t)w * 16, (size_t)h, cudaMemcpyHostToDevice));
+    cudaResourceDesc res;
+    memset(&res, 0, sizeof(res));
+    res.resType = cudaResourceTypeArray;
+    res.res.array.array = slot.array;
+    cudaTextureDesc td;
+    memset(&td, 0, sizeof(td));
+    td.addressMode[0] = td.addressMode[1] = cudaAddressModeBorder; // black outside, as Image::getPixel
+    td.filterMode = cudaFilterModePoint;                           // nearest texel
+    td.readMode = cudaReadModeElementType;
+    td.normalizedCoords = 0;
+    CU(cudaCreateTextureObject(&slot.point, &res, &td, nullptr));
+    td.filterMode = cudaFilterModeLinear;
+    CU(cudaCreateTextureObject(&slot.linear, &res, &td, nullptr));
+    slot.w = w, slot.h = h;
+    return PTB_OK;
+}
+
+int syncImageTable(PtbScene *s)
+{
+    std::vector<DevImage> table(s->images.size());
+    for(size_t i = 0; i < table.size(); i++)
+    {
+        table[i].tex = s->images[i].point;
+        table[i].texLinear = s->images[i].linear;
+        table[i].w = s->images[i].w;
+        table[i].h = s->images[i].h;
+    }
+    if((int)table.size() > s->imageCapacity)
+    {
+        int cap = std::max<int>(16, (int)table.size() * 2);
+        DevImage *p = nullptr;
+        CU(cudaMalloc((void **)&p, cap * sizeof(DevImage)));
+        s->allocs.push_back(p);
+        s->dImages = p;
+        s->imageCapacity = cap;
+    }
+    if(!table.empty())
+        CU(cudaMemcpy(s->dImages, table.data(), table.size() * sizeof(DevImage), cudaMemcpyHostToDevice));
+    s->dev.images = s->dImages;
+    s->dev.nImages = (int)table.size();
+    return PTB_OK;
+}
+
+// Checks a texture chain: wrappers then exactly one leaf, all arguments in range.
+int validateTexture(const PtbSceneDesc *d, int root)
+{
+    if(root < 0 || root >= d->n_texops)
+        return fail(PTB_EINVAL, "texture root out of range");
+    for(int i = root;; i++)
+    {
+        if(i >= d->n_texops)
+            return fail(PTB_EINVAL, "texture chain runs past the end of texops");
+        const PtbTexOp &op = d->texops[i];
+        switch(op.kind)
+        {
+        case PTB_TEX_CONST:
+        case PTB_TEX_MULTIPLY:
+            if(op.arg < 0 || op.arg + 3 > d->n_texdata)
+                return fail(PTB_EINVAL, "texture data offset out of range");
+            break;
+        case PTB_TEX_AFFINE:
+            if(op.arg < 0 || op.arg + 12 > d->n_texdata)
+                return fail(PTB_EINVAL, "texture matrix offset out of range");
+            break;
+        case PTB_TEX_IMAGE:
+        case PTB_TEX_IMAGE_ALPHA:
+            if(op.arg < 0)
+                return fail(PTB_EINVAL, "negative image index");
+            break;
+        case PTB_TEX_SKYBOX:
+        case PTB_TEX_SKYBOX_ALPHA:
+            if(op.arg < 0)
+                return fail(PTB_EINVAL, "negative image index");
+            break;
+        case PTB_TEX_LOG:
+        case PTB_TEX_MIRRORBALL:
+        case PTB_TEX_SPHERICAL:
+            break;
+        default:
+            return fail(PTB_EINVAL, "unknown texture op");
+        }
+        if(PTB_TEX_IS_LEAF(op.kind))
+            return PTB_OK;
+    }
+}
+} // namespace
+
+// ---- scene ------------------------------------------------------------------------------------
+extern "C" const char *ptb200_last_error(void) { return g_error.c_str(); }
+extern "C" int ptb200_abi_version(void) { return PTB200_ABI_VERSION; }
+extern "C" int ptb200_device_count(void)
+{
+    int n = 0;
+    if(cudaGetDeviceCount(&n) != cudaSuccess)
+        return 0;
+    return n;
+}
+
+static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s)
+{
+    if(!d || d->abi_version != PTB200_ABI_VERSION)
+        return fail(PTB_EINVAL, "scene description has a different abi_version");
+    if(d->n_prims <= 0 || d->n_ops <= 0 || d->n_materials <= 0)
+        return fail(PTB_EINVAL, "empty scene");
+    if(d->n_prims > 32767)
+        return fail(PTB_EINVAL, "more than 32767 primitives (boundary tags are 16 bits)");
+    int nDev = 0;
+    if(cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0)
+        return fail(PTB_ENODEV, "no CUDA device: libptb200 has no CPU fallback");
+    CU(cudaGetDevice(&s->device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, s->device));
+    s->smCount = prop.multiProcessorCount;
+    s->smemOptin = prop.sharedMemPerBlockOptin;
+
+    // validate tables
+    for(int i = 0; i < d->n_chains; i++)
+        if(d->chains[i].first < 0 || d->chains[i].count <= 0 || d->chains[i].first + d->chains[i].count > d->n_chain_xf)
+            return fail(PTB_EINVAL, "transform chain out of range");
+    for(int i = 0; i < d->n_chain_xf; i++)
+        if(d->chain_xf[i] < 0 || d->chain_xf[i] >= d->n_xforms)
+            return fail(PTB_EINVAL, "transform index out of range");
+    for(int i = 0; i < d->n_prims; i++)
+    {
+        const PtbPrim &p = d->prims[i];
+        if(p.type != PTB_PRIM_SPHERE && p.type != PTB_PRIM_PLANE)
+            return fail(PTB_EINVAL, "unknown primitive type");
+        if(p.material < 0 || p.material >= d->n_materials)
+            return fail(PTB_EINVAL, "primitive material out of range");
+        if(p.chain < -1 || p.chain >= d->n_chains)
+            return fail(PTB_EINVAL, "primitive chain out of range");
+    }
+    for(int i = 0; i < d->n_materials; i++)
+        for(int k = 0; k < 5; k++)
+            if(int rc = validateTexture(d, d->materials[i].tex[k]))
+                return rc;
+
+    // compile the postfix program into the 16-byte word stream of ptb_csg.cuh and find the
+    // deepest list stack and the worst-case span-pool use (every primitive hit, no merging)
+    std::vector<uint4> prog;
+    std::vector<int> sizes; // worst-case list length of each stack entry
+    int maxStack = 0, poolBound = 1, lastChain = -2;
+    for(int i = 0; i < d->n_ops; i++)
+    {
+        uint32_t op = d->ops[i];
+        uint32_t kind = PTB_OP_KIND(op);
+        if(kind == PTB_OP_PUSH_PRIM)
+        {
+            uint32_t prim = PTB_OP_ARG(op);
+            if((int)prim >= d->n_prims)
+                return fail(PTB_EINVAL, "PUSH_PRIM names a primitive out of range");
+            const PtbPrim &p = d->prims[prim];
+            int nchain = p.chain >= 0 ? d->chains[p.chain].count : 0;
+            bool reuse = p.chain >= 0 && p.chain == lastChain;
+            prog.push_back(make_uint4(p.type == PTB_PRIM_SPHERE ? DK_SPHERE : DK_PLANE, prim, (uint32_t)nchain, reuse ? PTB_LEAF_REUSE_RAY : 0u));
+            uint4 g;
+            memcpy(&g, p.p, 16);
+            prog.push_back(g);
+            if(!reuse)
+                for(int k = 0; k < nchain; k++)
+                {
+                    const PtbXform &x = d->xforms[d->chain_xf[d->chains[p.chain].first + k]];
+                    for(int r = 0; r < 3; r++)
+                    {
+                        uint4 row;
+                        memcpy(&row, x.m + 4 * r, 16);
+                        prog.push_back(row);
+                    }
+                }
+            lastChain = p.chain;
+            sizes.push_back(1);
+            int total = 0;
+            for(int v : sizes)
+                total += v;
+            poolBound = std::max(poolBound, total);
+        }
+        else if(kind == PTB_OP_UNION || kind == PTB_OP_DIFFERENCE || kind == PTB_OP_INTERSECTION)
+        {
+            if(sizes.size() < 2)
+                return fail(PTB_EINVAL, "CSG operator with fewer than two operands on the stack");
+            prog.push_back(make_uint4(kind == PTB_OP_UNION ? DK_UNION : kind == PTB_OP_DIFFERENCE ? DK_DIFFERENCE : DK_INTERSECTION, 0, 0, 0));
+            int total = 0;
+            for(int v : sizes)
+                total += v;
+            int lb = sizes.back();
+            sizes.pop_back();
+            int la = sizes.back();
+            sizes.pop_back();
+            poolBound = std::max(poolBound, total + la + lb); // merge output is appended, then moved down
+            sizes.push_back(la + lb);
+        }
+        else
+            return fail(PTB_EINVAL, "unknown CSG op");
+        maxStack = std::max(maxStack, (int)sizes.size());
+    }
+    if(sizes.size() != 1)
+        return fail(PTB_EINVAL, "CSG program does not leave exactly one object on the stack");
+    if(poolBound > 65535)
+        return fail(PTB_EINVAL, "scene too large for 16-bit span-pool offsets");
+    prog.push_back(make_uint4(DK_END, 0, 0, 0));
+
+    std::vector<float4> geo(d->n_prims);
+    std::vector<int4> meta(d->n_prims);
+    for(int i = 0; i < d->n_prims; i++)
+    {
+        const PtbPrim &p = d->prims[i];
+        geo[i] = make_float4(p.p[0], p.p[1], p.p[2], p.p[3]);
+        meta[i] = make_int4(p.type, p.material, p.chain >= 0 ? d->chains[p.chain].first : 0, p.chain >= 0 ? d->chains[p.chain].count : 0);
+    }
+    std::vector<float4> xf((size_t)d->n_xforms * 6);
+    for(int i = 0; i < d->n_xforms; i++)
+    {
+        memcpy(&xf[6 * (size_t)i], d->xforms[i].m, 48);
+        memcpy(&xf[6 * (size_t)i + 3], d->xforms[i].inv, 48);
+    }
+    std::vector<int> chainXf(d->chain_xf, d->chain_xf + d->n_chain_xf);
+    std::vector<DevMaterial> mats(d->n_materials);
+    for(int i = 0; i < d->n_materials; i++)
+    {
+        for(int k = 0; k < 5; k++)
+            mats[i].tex[k] = d->materials[i].tex[k];
+        mats[i].ior = d->materials[i].ior;
+        mats[i].iorIn = (float)(1.0 / d->materials[i].ior); // `ior = 1.0 / material->ior`, path-trace.h:79
+        mats[i].pad = 0;
+    }
+    std::vector<int2> texops(d->n_texops);
+    for(int i = 0; i < d->n_texops; i++)
+        texops[i] = make_int2(d->texops[i].kind, d->texops[i].arg);
+    std::vector<float> texdata(d->texdata, d->texdata + d->n_texdata);
+
+    DevScene &dev = s->dev;
+    memset(&dev, 0, sizeof(dev));
+    int rc;
+    if((rc = upload(s, prog, &dev.program)) || (rc = upload(s, geo, &dev.primGeo)) || (rc = upload(s, meta, &dev.primMeta)) ||
+       (rc = upload(s, chainXf, &dev.chainXf)) || (rc = upload(s, xf, &dev.xforms)) || (rc = upload(s, mats, &dev.materials)) ||
+       (rc = upload(s, texops, &dev.texops)) || (rc = upload(s, texdata, &dev.texdata)))
+        return rc;
+    dev.programWords = (int)prog.size();
+    dev.nPrims = d->n_prims, dev.nMaterials = d->n_materials, dev.nTexops = d->n_texops;
+    dev.maxStack = maxStack, dev.poolBound = poolBound;
+    for(int i = 0; i < d->n_images; i++)
+    {
+        ImageSlot slot;
+        if((rc = createImage(d->images[i].rgba, d->images[i].width, d->images[i].height, slot)))
+            return rc;
+        s->images.push_back(slot);
+    }
+    return syncImageTable(s);
+}
+
+extern "C" void ptb200_scene_destroy(PtbScene *s)
+{
+    if(!s)
+        return;
+    cudaSetDevice(s->device);
+    for(ImageSlot &im : s->images)
+    {
+        if(im.point)
+            cudaDestroyTextureObject(im.point);
+        if(im.linear)
+            cudaDestroyTextureObject(im.linear);
+        if(im.array)
+            cudaFreeArray(im.array);
+    }
+    for(void *p : s->allocs)
+        cudaFree(p);
+    delete s;
+}
+
+extern "C" int ptb200_scene_create(const PtbSceneDesc *desc, PtbScene **out)
+{
+    if(!out)
+        return fail(PTB_EINVAL, "null output pointer");
+    *out = nullptr;
+    try
+    {
+        PtbScene *s = new PtbScene;
+        int rc = sceneCreateImpl(desc, s);
+        if(rc)
+        {
+            std::string keep = g_error;
+            ptb200_scene_destroy(s);
+            g_error = keep;
+            return rc;
+        }
+        *out = s;
+        return PTB_OK;
+    }
+    catch(std::bad_alloc &)
+    {
+        return fail(PTB_ENOMEM, "out of host memory");
+    }
+    catch(std::exception &e)
+    {
+        return fail(PTB_EINVAL, e.what());
+    }
+}
+
+extern "C" int ptb200_image_upload(PtbScene *s, const float *rgba, int width, int height, int *handle)
+{
+    if(!s || !handle)
+        return fail(PTB_EINVAL, "null argument");
+    std::lock_guard<std::mutex> g(s->lock);
+    CU(cudaSetDevice(s->device));
+    ImageSlot slot;
+    if(int rc = createImage(rgba, width, height, slot))
+        return rc;
+    s->images.push_back(slot);
+    *handle = (int)s->images.size() - 1;
+    return syncImageTable(s);
+}
+
+// ---- launch configuration -----------------------------------------------------------------------
+// Persistent grid: (resident CTAs per SM) x (SM count).  The span pool keeps `cap` slots per
+// thread in shared memory; scenes whose worst case needs more get a global overflow area.
+static int chooseConfig(PtbScene *s, int which, DeviceBuffer &overflow, CsgConfig &cfg)
+{
+    const DevScene &dev = s->dev;
+    cfg.threads = 128;
+    int cap = std::min(dev.poolBound, 16);
+    if(const char *e = getenv("PTB200_POOL_CAP"))
+        cap = std::max(2, std::min(dev.poolBound, atoi(e)));
+    cfg.cap = cap;
+    cfg.stageProgram = (size_t)dev.programWords * 16 <= 64 * 1024 ? 1 : 0;
+    cfg.smemBytes = csgSharedBytes(dev, cfg.threads, cfg.cap, cfg.stageProgram);
+    if(cfg.smemBytes > s->smemOptin)
+        return fail(PTB_EINVAL, "scene needs more shared memory per CTA than the device offers");
+    int perSm = csgBlocksPerSm(which, cfg.threads, cfg.smemBytes);
+    if(perSm <= 0)
+        return fail(PTB_ECUDA, "kernel does not fit on an SM with this shared-memory size");
+    if(const char *e = getenv("PTB200_BLOCKS_PER_SM"))
+        perSm = std::max(1, std::min(perSm, atoi(e)));
+    cfg.blocks = perSm * s->smCount;
+    cfg.ovfStride = (size_t)cfg.blocks * cfg.threads;
+    cfg.overflow = nullptr;
+    if(dev.poolBound > cfg.cap)
+    {
+        size_t bytes = (size_t)(dev.poolBound - cfg.cap) * 3 * sizeof(float) * cfg.ovfStride;
+        CU(overflow.ensure(bytes));
+        cfg.overflow = (float *)overflow.p;
+    }
+    return PTB_OK;
+}
+
+// ---- ray-batch intersection -----------------------------------------------------------------------
+extern "C" int ptb200_intersect_device(PtbScene *s, const void *d_origins4, const void *d_dirs4, size_t n, void *d_hits, void *d_spans, int max_spans, uint32_t flags,
+                                       void *stream)
+{
+    if(!s || !d_origins4 || !d_dirs4 || !d_hits)
+        return fail(PTB_EINVAL, "null argument");
+    if(d_spans && max_spans <= 0)
+        return fail(PTB_EINVAL, "max_spans must be positive when spans are requested");
+    std::lock_guard<std::mutex> g(s->lock);
+    CU(cudaSetDevice(s->device));
+    CsgConfig cfg;
+    bool exact = flags & PTB_FLAG_EXACT;
+    if(int rc = chooseConfig(s, exact ? 1 : 0, s->scratch.overflow, cfg))
+        return rc;
+    if(n == 0)
+        return PTB_OK;
+    launchIntersect(s->dev, cfg, (const float4 *)d_origins4, (const float4 *)d_dirs4, n, (PtbHit *)d_hits, (PtbSpan *)d_spans, max_spans, exact, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return PTB_OK;
+}
+
+extern "C" int ptb200_intersect(PtbScene *s, const float *origins, const float *dirs, size_t n, PtbHit *hits, PtbSpan *spans, int max_spans, uint32_t flags)
+{
+    if(!s || (n && (!origins || !dirs || !hits)))
+        return fail(PTB_EINVAL, "null argument");
+    if(n == 0)
+        return PTB_OK;
+    try
+    {
+        CU(cudaSetDevice(s->device));
+        std::vector<float4> o4(n), d4(n);
+        for(size_t i = 0; i < n; i++)
+        {
+            o4[i] = make_float4(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2], 0.f);
+            d4[i] = make_float4(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2], 0.f);
+        }
+        DeviceBuffer bo, bd, bh, bs;
+        CU(bo.ensure(n * 16));
+        CU(bd.ensure(n * 16));
+        CU(bh.ensure(n * sizeof(PtbHit)));
+        if(spans)
+            CU(bs.ensure(n * (size_t)max_spans * sizeof(PtbSpan)));
+        CU(cudaMemcpy(bo.p, o4.data(), n * 16, cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(bd.p, d4.data(), n * 16, cudaMemcpyHostToDevice));
+        if(spans)
+            CU(cudaMemset(bs.p, 0, n * (size_t)max_spans * sizeof(PtbSpan)));
+        if(int rc = ptb200_intersect_device(s, bo.p, bd.p, n, bh.p, spans ? bs.p : nullptr, max_spans, flags, nullptr))
+            return rc;
+        CU(cudaDeviceSynchronize());
+        CU(cudaMemcpy(hits, bh.p, n * sizeof(PtbHit), cudaMemcpyDeviceToHost));
+        if(spans)
+            CU(cudaMemcpy(spans, bs.p, n * (size_t)max_spans * sizeof(PtbSpan), cudaMemcpyDeviceToHost));
+        return PTB_OK;
+    }
+    catch(std::bad_alloc &)
+    {
+        return fail(PTB_ENOMEM, "out of host memory");
+    }
+}
+
+// ---- inspection entry points ------------------------------------------------------------------------
+extern "C" int ptb200_texture_eval(PtbScene *s, int tex_root, const float *positions, size_t n, float *rgb, float *f, uint32_t flags)
+{
+    if(!s || (n && !positions))
+        return fail(PTB_EINVAL, "null argument");
+    if(tex_root < 0 || tex_root >= s->dev.nTexops)
+        return fail(PTB_EINVAL, "texture root out of range");
+    if(n == 0)
+        return PTB_OK;
+    std::lock_guard<std::mutex> g(s->lock);
+    CU(cudaSetDevice(s->device));
+    DeviceBuffer bp, bc, bf;
+    CU(bp.ensure(n * 12));
+    CU(bc.ensure(n * 12));
+    CU(bf.ensure(n * 4));
+    CU(cudaMemcpy(bp.p, positions, n * 12, cudaMemcpyHostToDevice));
+    launchTextureEval(s->dev, tex_root, (const float *)bp.p, n, (float *)bc.p, (float *)bf.p, flags, nullptr);
+    CU(cudaGetLastError());
+    CU(cudaDeviceSynchronize());
+    if(rgb)
+        CU(cudaMemcpy(rgb, bc.p, n * 12, cudaMemcpyDeviceToHost));
+    if(f)
+        CU(cudaMemcpy(f, bf.p, n * 4, cudaMemcpyDeviceToHost));
+    return PTB_OK;
+}
+
+extern "C" int ptb200_sample_scatter(const float *normal, const float *mirror, float scatter, size_t n, uint64_t seed, uint32_t flags, float *dirs)
+{
+    if(!normal || !mirror || !dirs)
+        return fail(PTB_EINVAL, "null argument");
+    int nDev = 0;
+    if(cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0)
+        return fail(PTB_ENODEV, "no CUDA device: libptb200 has no CPU fallback");
+    DeviceBuffer b;
+    CU(b.ensure(n * 12));
+    launchScatterSample(normal, mirror, scatter, n, seed, flags, (float *)b.p, nullptr);
+    CU(cudaGetLastError());
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(dirs, b.p, n * 12, cudaMemcpyDeviceToHost));
+    return PTB_OK;
+}
+
+extern "C" int ptb200_fp32_peak(double *fma_per_second, double *sm_clock_mhz)
+{
+    int nDev = 0, dev = 0;
+    if(cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0)
+        return fail(PTB_ENODEV, "no CUDA device: libptb200 has no CPU fallback");
+    CU(cudaGetDevice(&dev));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, dev));
+    cudaEvent_t a, b;
+    CU(cudaEventCreate(&a));
+    CU(cudaEventCreate(&b));
+    int blocks = prop.multiProcessorCount * 8;
+    launchFmaPeak(blocks, 256, 64, nullptr); // warm-up
+    double best = 0;
+    for(int rep = 0; rep < 5; rep++)
+    {
+        CU(cudaEventRecord(a));
+        double fmas = launchFmaPeak(blocks, 256, 4096, nullptr);
+        CU(cudaEventRecord(b));
+        CU(cudaEventSynchronize(b));
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, a, b));
+        best = std::max(best, fmas / (ms * 1e-3));
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    if(fma_per_second)
+        *fma_per_second = best;
+    if(sm_clock_mhz)
+        *sm_clock_mhz = best / ((double)prop.multiProcessorCount * 128.0) * 1e-6; // implied clock at 128 lanes/SM
+    return PTB_OK;
+}
+
+// ---- wavefront render driver ------------------------------------------------------------------------
+static int checkParams(const PtbRenderParams *p, int &x0, int &y0, int &rw, int &rh)
+{
+    if(!p)
+        return fail(PTB_EINVAL, "null render params");
+    if(p->width <= 0 || p->height <= 0 || (long long)p->width * p->height > (1ll << 31) - 1)
+        return fail(PTB_EINVAL, "bad image size");
+    if(p->spp <= 0 || p->sample_stride <= 0 || p->sample_offset < 0 || p->max_depth < 0 || p->max_depth > 255)
+        return fail(PTB_EINVAL, "bad sample count / stride / depth");
+    x0 = p->x0, y0 = p->y0;
+    int x1 = p->x1, y1 = p->y1;
+    if(x0 == 0 && y0 == 0 && x1 == 0 && y1 == 0)
+        x1 = p->width, y1 = p->height;
+    if(x0 < 0 || y0 < 0 || x1 > p->width || y1 > p->height || x1 <= x0 || y1 <= y0)
+        return fail(PTB_EINVAL, "bad pixel rectangle");
+    rw = x1 - x0, rh = y1 - y0;
+    return PTB_OK;
+}
+
+// Caller holds scene->lock and has made scene->device current.
+static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbStats *stats, cudaStream_t stream)
+{
+    int x0, y0, rw, rh;
+    if(int rc = checkParams(p, x0, y0, rw, rh))
+        return rc;
+    RenderScratch &sx = s->scratch;
+    CsgConfig cfg;
+    if(int rc = chooseConfig(s, 2, sx.overflow, cfg))
+        return rc;
+    const size_t nPix = (size_t)rw * rh;
+    int perPass = p->samples_per_pass;
+    if(perPass <= 0)
+        perPass = (int)std::max<size_t>(1, (size_t(8) << 20) / nPix);
+    perPass = std::min(perPass, p->spp);
+    const size_t capacity = nPix * (size_t)perPass;
+    if(capacity > 0xFFFFFFF0ull)
+        return fail(PTB_EINVAL, "samples_per_pass x pixels exceeds the 32-bit queue index");
+    const int nPasses = (p->spp + perPass - 1) / perPass;
+    const int stages = p->max_depth + 1; // primary + max_depth bounces
+    CU(sx.queues.ensure(capacity * 64 * 2));
+    CU(sx.counters.ensure((size_t)nPasses * (stages + 1) * sizeof(unsigned)));
+    CU(cudaMemsetAsync(sx.counters.p, 0, (size_t)nPasses * (stages + 1) * sizeof(unsigned), stream));
+    RayQueue q[2];
+    for(int k = 0; k < 2; k++)
+    {
+        float4 *base = (float4 *)sx.queues.p + (size_t)k * capacity * 4;
+        q[k].q0 = base, q[k].q1 = base + capacity, q[k].q2 = base + 2 * capacity, q[k].q3 = base + 3 * capacity;
+    }
+    const bool timed = stats != nullptr;
+    size_t nEvents = timed ? (size_t)nPasses * 3 : 0;
+    while(sx.events.size() < nEvents)
+    {
+        cudaEvent_t e;
+        CU(cudaEventCreate(&e));
+        sx.events.push_back(e);
+    }
+    RenderPass pass;
+    pass.width = p->width, pass.height = p->height;
+    pass.x0 = x0, pass.y0 = y0, pass.rw = rw, pass.rh = rh;
+    pass.sampleStride = p->sample_stride;
+    pass.maxDepth = p->max_depth;
+    pass.sw = p->screen_width, pass.sh = p->screen_height, pass.sd = p->screen_distance;
+    pass.seed = p->seed;
+    pass.flags = p->flags;
+    uint64_t launches = 0;
+    for(int i = 0; i < nPasses; i++)
+    {
+        unsigned *c = (unsigned *)sx.counters.p + (size_t)i * (stages + 1);
+        pass.samplesThisPass = std::min(perPass, p->spp - i * perPass);
+        pass.sampleBase = p->sample_offset + i * perPass * p->sample_stride;
+        if(timed)
+            CU(cudaEventRecord(sx.events[3 * i], stream));
+        launchPrimary(s->dev, cfg, pass, accum, q[0], c, stream);
+        if(timed)
+            CU(cudaEventRecord(sx.events[3 * i + 1], stream));
+        for(int b = 1; b <= p->max_depth; b++)
+            launchBounce(s->dev, cfg, pass, accum, q[(b - 1) & 1], c + (b - 1), q[b & 1], c + b, stream);
+        if(timed)
+            CU(cudaEventRecord(sx.events[3 * i + 2], stream));
+        launches += 1 + p->max_depth;
+        CU(cudaGetLastError());
+    }
+    if(!timed)
+        return PTB_OK;
+    size_t nCounters = (size_t)nPasses * (stages + 1);
+    if(sx.hostCountersLen < nCounters)
+    {
+        if(sx.hostCounters)
+            cudaFreeHost(sx.hostCounters);
+        sx.hostCounters = nullptr;
+        CU(cudaMallocHost((void **)&sx.hostCounters, nCounters * sizeof(unsigned)));
+        sx.hostCountersLen = nCounters;
+    }
+    CU(cudaMemcpyAsync(sx.hostCounters, sx.counters.p, nCounters * sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
+    CU(cudaStreamSynchronize(stream));
+    memset(stats, 0, sizeof(*stats));
+    stats->launches = launches;
+    for(int i = 0; i < nPasses; i++)
+    {
+        const unsigned *c = sx.hostCounters + (size_t)i * (stages + 1);
+        uint64_t primary = nPix * (uint64_t)std::min(perPass, p->spp - i * perPass);
+        stats->paths += primary;
+        stats->rays_primary += primary;
+        stats->queue_bytes += 64ull * c[0];
+        for(int b = 1; b <= p->max_depth; b++)
+        {
+            stats->rays_bounce += c[b - 1];
+            stats->queue_bytes += 64ull * c[b - 1] + 64ull * c[b];
+        }
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, sx.events[3 * i], sx.events[3 * i + 1]));
+        stats->ms_primary += ms;
+        CU(cudaEventElapsedTime(&ms, sx.events[3 * i + 1], sx.events[3 * i + 2]));
+        stats->ms_bounce += ms;
+    }
+    stats->rays = stats->rays_primary + stats->rays_bounce;
+    float total = 0;
+    CU(cudaEventElapsedTime(&total, sx.events[0], sx.events[3 * (size_t)(nPasses - 1) + 2]));
+    stats->ms_total = total;
+    return PTB_OK;
+}
+
+extern "C" int ptb200_render_accumulate_device(PtbScene *s, const PtbRenderParams *p, void *d_accum4, PtbStats *stats, void *stream)
+{
+    if(!s || !d_accum4)
+        return fail(PTB_EINVAL, "null argument");
+    std::lock_guard<std::mutex> g(s->lock);
+    if(s->asyncBusy)
+        return fail(PTB_EBUSY, "an asynchronous render is running on this scene");
+    CU(cudaSetDevice(s->device));
+    return renderPasses(s, p, (float4 *)d_accum4, stats, (cudaStream_t)stream);
+}
+
+extern "C" int ptb200_resolve_device(const void *d_accum4, void *d_rgba4, size_t n_pixels, void *stream)
+{
+    if(!d_accum4 || !d_rgba4)
+        return fail(PTB_EINVAL, "null argument");
+    if(n_pixels == 0)
+        return PTB_OK;
+    launchResolve((const float4 *)d_accum4, (float4 *)d_rgba4, n_pixels, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return PTB_OK;
+}
+
+extern "C" int ptb200_render(PtbScene *s, const PtbRenderParams *p, float *rgba_out, PtbStats *stats)
+{
+    if(!s || !rgba_out)
+        return fail(PTB_EINVAL, "null argument");
+    int x0, y0, rw, rh;
+    if(int rc = checkParams(p, x0, y0, rw, rh))
+        return rc;
+    std::lock_guard<std::mutex> g(s->lock);
+    if(s->asyncBusy)
+        return fail(PTB_EBUSY, "an asynchronous render is running on this scene");
+    CU(cudaSetDevice(s->device));
+    size_t nPix = (size_t)p->width * p->height;
+    CU(s->scratch.accum.ensure(nPix * 16));
+    float4 *accum = (float4 *)s->scratch.accum.p;
+    CU(cudaMemsetAsync(accum, 0, nPix * 16, nullptr));
+    PtbStats local;
+    if(int rc = renderPasses(s, p, accum, stats ? stats : &local, nullptr))
+        return rc;
+    cudaEvent_t a, b;
+    CU(cudaEventCreate(&a));
+    CU(cudaEventCreate(&b));
+    CU(cudaEventRecord(a, nullptr));
+    launchResolve(accum, accum, nPix, nullptr);
+    CU(cudaEventRecord(b, nullptr));
+    CU(cudaGetLastError());
+    // only the rendered rectangle is written to the caller's buffer
+    CU(cudaMemcpy2D(rgba_out + 4 * ((size_t)y0 * p->width + x0), (size_t)p->width * 16, accum + (size_t)y0 * p->width + x0, (size_t)p->width * 16, (size_t)rw * 16,
+                    (size_t)rh, cudaMemcpyDeviceToHost));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    if(stats)
+    {
+        stats->ms_resolve = ms;
+        stats->launches += 1;
+    }
+    return PTB_OK;
+}
+
+// ---- asynchronous / progressive boundary (BlockRenderer::done / copyToBuffer) -----------------------
+static void jobMain(PtbJob *job)
+{
+    PtbScene *s = job->scene;
+    {
+        std::lock_guard<std::mutex> g(s->lock);
+        cudaSetDevice(s->device);
+        cudaStream_t stream = nullptr;
+        int rc = cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking) == cudaSuccess ? PTB_OK : PTB_ECUDA;
+        if(rc == PTB_OK)
+            rc = renderPasses(s, &job->params, job->accum, &job->stats, stream);
+        if(rc != PTB_OK)
+            job->error = rc == PTB_ECUDA && g_error.empty() ? "cudaStreamCreate failed" : g_error;
+        if(stream)
+        {
+            cudaStreamSynchronize(stream);
+            cudaStreamDestroy(stream);
+        }
+        job->status = rc;
+        s->asyncBusy = false;
+    }
+    __sync_synchronize();
+    job->done = 1;
+}
+
+extern "C" int ptb200_render_async(PtbScene *s, const PtbRenderParams *p, PtbJob **out)
+{
+    if(!s || !out)
+        return fail(PTB_EINVAL, "null argument");
+    *out = nullptr;
+    int x0, y0, rw, rh;
+    if(int rc = checkParams(p, x0, y0, rw, rh))
+        return rc;
+    PtbJob *job = nullptr;
+    {
+        std::lock_guard<std::mutex> g(s->lock);
+        if(s->asyncBusy)
+            return fail(PTB_EBUSY, "an asynchronous render is already running on this scene");
+        CU(cudaSetDevice(s->device));
+        job = new PtbJob;
+        job->scene = s;
+        job->params = *p;
+        size_t nPix = (size_t)p->width * p->height;
+        if(cudaMalloc((void **)&job->accum, nPix * 16) != cudaSuccess || cudaMemset(job->accum, 0, nPix * 16) != cudaSuccess ||
+           cudaStreamCreateWithFlags(&job->readStream, cudaStreamNonBlocking) != cudaSuccess)
+        {
+            if(job->accum)
+                cudaFree(job->accum);
+            delete job;
+            return fail(PTB_ECUDA, "could not allocate the job's accumulation buffer");
+        }
+        s->asyncBusy = true;
+    }
+    job->worker = std::thread(jobMain, job);
+    *out = job;
+    return PTB_OK;
+}
+
+extern "C" int ptb200_job_done(PtbJob *job)
+{
+    if(!job)
+        return fail(PTB_EINVAL, "null job");
+    if(!job->done)
+        return 0;
+    if(job->status != PTB_OK)
+        return fail(job->status, job->error);
+    return 1;
+}
+
+extern "C" int ptb200_job_read(PtbJob *job, float *rgba, int width, int height)
+{
+    if(!job || !rgba)
+        return fail(PTB_EINVAL, "null argument");
+    if(width != job->params.width || height != job->params.height)
+        return fail(PTB_EINVAL, "buffer size differs from the job's image size");
+    CU(cudaSetDevice(job->scene->device));
+    size_t nPix = (size_t)width * height;
+    job->staging.resize(nPix * 4);
+    CU(cudaMemcpyAsync(job->staging.data(), job->accum, nPix * 16, cudaMemcpyDeviceToHost, job->readStream));
+    CU(cudaStreamSynchronize(job->readStream));
+    const float *a = job->staging.data();
+    for(size_t i = 0; i < nPix; i++)
+        if(a[4 * i + 3] > 0.f)
+        { // only valid pixels are written, as RenderBlock::copyToBuffer (src/test.cpp:359-371)
+            float inv = 1.f / a[4 * i + 3];
+            rgba[4 * i] = a[4 * i] * inv, rgba[4 * i + 1] = a[4 * i + 1] * inv, rgba[4 * i + 2] = a[4 * i + 2] * inv, rgba[4 * i + 3] = 1.f;
+        }
+    return PTB_OK;
+}
+
+extern "C" int ptb200_job_wait(PtbJob *job, PtbStats *stats)
+{
+    if(!job)
+        return fail(PTB_EINVAL, "null job");
+    if(job->worker.joinable())
+        job->worker.join();
+    if(stats)
+        *stats = job->stats;
+    if(job->status != PTB_OK)
+        return fail(job->status, job->error);
+    return PTB_OK;
+}
+
+extern "C" void ptb200_job_destroy(PtbJob *job)
+{
+    if(!job)
+        return;
+    if(job->worker.joinable())
+        job->worker.join();
+    cudaSetDevice(job->scene->device);
+    if(job->readStream)
+        cudaStreamDestroy(job->readStream);
+    if(job->accum)
+        cudaFree(job->accum);
+    delete job;
+}

@@ -195,7 +195,7 @@ struct MergeCursor
 
 // Runs one combinator to exhaustion, writing its output spans from `dst` on; returns the slot
 // after the last output.
-__device__ __noinline__ int mergeLists(const Pool &pool, int kind, int a0, int b0, int top, int dst)
+static __device__ __noinline__ int mergeLists(const Pool &pool, int kind, int a0, int b0, int top, int dst)
 {
     MergeCursor m(pool, a0, b0, top, dst);
     m.nextA();

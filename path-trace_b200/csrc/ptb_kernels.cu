@@ -387,3 +387,34 @@ double launchFmaPeak(int blocks, int threads, int iters, cudaStream_t stream)
 }
 
 } // namespace ptb
+
+namespace ptb
+{
+// Resident CTAs per SM for a CSG kernel at this shared-memory size (occupancy API).
+int csgBlocksPerSm(int which, int threads, size_t smemBytes)
+{
+    int n = 0;
+    cudaError_t e;
+    if(which == 0)
+    {
+        cudaFuncSetAttribute(intersectKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, intersectKernel<false>, threads, smemBytes);
+    }
+    else if(which == 1)
+    {
+        cudaFuncSetAttribute(intersectKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, intersectKernel<true>, threads, smemBytes);
+    }
+    else
+    {
+        cudaFuncSetAttribute(primaryKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, primaryKernel, threads, smemBytes);
+    }
+    if(e != cudaSuccess)
+    {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+} // namespace ptb

@@ -56,3 +56,9 @@ double launchFmaPeak(int blocks, int threads, int iters, cudaStream_t stream);
 size_t csgSharedBytes(const DevScene &sc, int threads, int cap, bool stageProgram);
 
 } // namespace ptb
+
+namespace ptb
+{
+// which: 0 = intersect (fast), 1 = intersect (exact), 2 = render stages
+int csgBlocksPerSm(int which, int threads, size_t smemBytes);
+}

@@ -111,6 +111,14 @@ int Flattener::findMaterial(const void *key) const
     return it == impl->materialIndex.end() ? -1 : it->second;
 }
 
+std::vector<const void *> Flattener::materialKeys() const
+{
+    std::vector<const void *> keys(impl->materials.size(), (const void *)NULL);
+    for(std::map<const void *, int>::const_iterator it = impl->materialIndex.begin(); it != impl->materialIndex.end(); ++it)
+        keys[it->second] = it->first;
+    return keys;
+}
+
 int Flattener::beginMaterial(const void *key, float ior)
 {
     PtbMaterial m;

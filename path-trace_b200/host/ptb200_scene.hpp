@@ -322,6 +322,7 @@ public:
     void addOp(int kind);
     // material / texture side
     int findMaterial(const void *key) const; // -1 if this Material* has not been flattened yet
+    std::vector<const void *> materialKeys() const; // the key behind each material index
     int beginMaterial(const void *key, float ior);
     void beginTexture(int material_index, int slot);
     void addTexOp(int kind, const float *data, int n_data);
