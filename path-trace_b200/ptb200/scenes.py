@@ -201,3 +201,72 @@ def config1(b, env=None):
         b.sphere((-1, 0, -4), 0.2, diffuse_white),
     ] + sky_planes(b, sky) + [make_lens(b, (-2.5 / 4, 0, -2.5), (-1, 0, -4), 0.5, 1.0, glass)]
     return b.union_array(objs)
+
+
+# ---- fuzz scenes: random CSG trees over spheres / planes, optional nested transforms -------------------
+def random_tree(b, seed, n_leaves=6, transforms=True, emissive=True):
+    """Random Union/Difference/Intersection tree.  Every primitive gets its own material (so a
+    material index identifies the primitive on the reference side, which has no primitive ids).
+    Primitives crowd the z axis so axis-parallel rays produce every merge branch, including
+    shared endpoints (quirk Q5) and the inverted Difference span (quirk Q4)."""
+    rs = np.random.RandomState(seed)
+    grid = [-2.0, -1.5, -1.0, -0.5, 0.0, 0.5, 1.0, 1.5, 2.0]
+
+    def material(i):
+        e = b.color(0.1 * (i + 1), 0.05 * (i + 1), 1.0 / (i + 1)) if emissive else b.color(0)
+        kind = rs.randint(4)
+        if kind == 0:
+            return b.material(b.color(0.8), b.color(1), e)
+        if kind == 1:
+            return b.material(b.color(0.9), b.color(float(rs.choice([0.0, 0.05, 0.3]))), e)
+        if kind == 2:
+            return b.material(b.color(0.7), b.color(0), e, b.color(0.9), 1.3, b.color(1))
+        return b.material(b.color(0.6, 0.7, 0.8), b.color(0.5), e, b.color(0.5), 1.5, b.color(0.4))
+
+    def leaf(i):
+        m = material(i)
+        if rs.rand() < 0.75:
+            c = (float(rs.choice([0.0, 0.0, 0.25])), float(rs.choice([0.0, 0.0, -0.25])), float(rs.choice(grid)) - 6.0)
+            obj = b.sphere(c, float(rs.choice([0.5, 0.75, 1.0, 1.25])), m)
+        else:
+            n = [(0, 0, 1), (0, 0, -1), (0, 1, 0), (1, 0, 0.5)][rs.randint(4)]
+            obj = b.plane_at(n, (0.0, 0.0, float(rs.choice(grid)) - 6.0), m)
+        if transforms and rs.rand() < 0.4:
+            obj = b.transformed(random_matrix(b, rs), obj)
+        return obj
+
+    def build(lo, hi):
+        if hi - lo == 1:
+            return leaf(lo)
+        mid = lo + 1 + rs.randint(hi - lo - 1)
+        a, c = build(lo, mid), build(mid, hi)
+        node = [b.union, b.difference, b.intersection][rs.randint(3)](a, c)
+        if transforms and rs.rand() < 0.2:
+            node = b.transformed(random_matrix(b, rs), node)
+        return node
+
+    return build(0, n_leaves)
+
+
+def random_matrix(b, rs):
+    """A mild world->object matrix: small rotation about a random axis, near-unit scale, small shift."""
+    axis = rs.normal(size=3)
+    axis /= np.linalg.norm(axis)
+    m = b.rotate(tuple(float(v) for v in axis), float(rs.uniform(-0.3, 0.3)))
+    m = b.concat(m, b.scale(*[float(v) for v in rs.choice([1.0, 1.0, 0.8, 1.25], 3)]))
+    return b.concat(m, b.translate(*[float(v) for v in rs.choice([0.0, 0.0, 0.25, -0.5], 3)]))
+
+
+def fuzz_rays(n, seed):
+    """Half axis-parallel rays down -z through the crowded axis (exact shared endpoints), half
+    random rays from in and around the cluster; mixed direction magnitudes (quirk Q1)."""
+    rs = np.random.RandomState(seed)
+    o = np.zeros((n, 3), np.float32)
+    d = np.zeros((n, 3), np.float32)
+    half = n // 2
+    o[:half] = np.stack([rs.choice([0.0, 0.25, 0.5], half), rs.choice([0.0, -0.25, 0.5], half), rs.choice([0.0, -4.0, -5.5, -6.0, -7.25], half)], 1)
+    d[:half] = np.stack([np.zeros(half), np.zeros(half), rs.choice([-1.0, 1.0, -2.0, -0.5, -2400.0], half)], 1)
+    o[half:] = rs.uniform(-3, 3, (n - half, 3)) + np.array([0, 0, -6.0])
+    v = rs.normal(size=(n - half, 3))
+    d[half:] = v * rs.choice([0.01, 1.0, 1.0, 100.0], (n - half, 1))
+    return o, d
