@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "ptb_launch.h"
+#include "ptb_csg_fast.cuh"
 
 using namespace ptb;
 
@@ -65,7 +66,7 @@ struct ImageSlot
 // Per-scene scratch for rendering (queues, counters, events); guarded by `busy`.
 struct RenderScratch
 {
-    DeviceBuffer queues, counters, overflow, accum;
+    DeviceBuffer queues, hits, counters, overflow, accum;
     unsigned *hostCounters = nullptr; // pinned
     size_t hostCountersLen = 0;
     std::vector<cudaEvent_t> events;
@@ -229,6 +230,123 @@ extern "C" int ptb200_device_count(void)
     return n;
 }
 
+// Compiles the (validated) postfix program for the fast evaluator, ptb_csg_fast.cuh: chains folded
+// into one matrix per leaf in double precision, planes moved to world space, the operator after a
+// leaf stored as the leaf's action, further operators packed behind it, and a SKIP word before the
+// right operand of every Difference / Intersection.
+static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out)
+{
+    auto f2u = [](float f) {
+        uint32_t u;
+        memcpy(&u, &f, 4);
+        return u;
+    };
+    // where does each operand start?  skipEnd[j] = index of the Difference/Intersection whose
+    // right operand starts at postfix position j
+    std::vector<int> skipEnd(d->n_ops, -1), first;
+    for(int i = 0; i < d->n_ops; i++)
+    {
+        if(PTB_OP_KIND(d->ops[i]) == PTB_OP_PUSH_PRIM)
+        {
+            first.push_back(i);
+            continue;
+        }
+        int b = first.back();
+        first.pop_back();
+        if(PTB_OP_KIND(d->ops[i]) != PTB_OP_UNION)
+            skipEnd[b] = i;
+    }
+    std::vector<size_t> skipWord(d->n_ops, 0); // SKIP word to patch when op i has been emitted
+    size_t header = 0; // word that can still take operators
+    bool sealed = true, freshLeaf = false;
+    for(int i = 0; i < d->n_ops; i++)
+    {
+        uint32_t op = d->ops[i], kind = PTB_OP_KIND(op);
+        if(kind != PTB_OP_PUSH_PRIM)
+        {
+            uint32_t code = kind == PTB_OP_UNION ? 0u : kind == PTB_OP_DIFFERENCE ? 1u : 2u;
+            if(freshLeaf && !sealed)
+                out[header].x |= (code + FA_UNION) << 4; // the leaf's action
+            else
+            {
+                uint32_t n = sealed ? PTB_FAST_MAX_POST : (out[header].x >> 8) & 15u;
+                if(n >= PTB_FAST_MAX_POST)
+                {
+                    out.push_back(make_uint4(FK_OPS, 0, 0, 0));
+                    header = out.size() - 1;
+                    sealed = false;
+                    n = 0;
+                }
+                out[header].x |= code << (12 + 2 * n);
+                out[header].x = (out[header].x & ~0xF00u) | ((n + 1) << 8);
+            }
+            freshLeaf = false;
+            if(kind != PTB_OP_UNION)
+            { // the right operand ends here: close the skipped region
+                size_t w = skipWord[i];
+                out[w].x = FK_SKIP | (uint32_t)((out.size() - (w + 1)) << 4);
+                sealed = true;
+            }
+            continue;
+        }
+        if(skipEnd[i] >= 0)
+        {
+            out.push_back(make_uint4(FK_SKIP, 0, 0, 0));
+            skipWord[skipEnd[i]] = out.size() - 1;
+        }
+        uint32_t prim = PTB_OP_ARG(op);
+        const PtbPrim &p = d->prims[prim];
+        // M = M_k ... M_1 (chain_xf lists the outermost wrapper, applied first, first)
+        double M[3][4] = {{1, 0, 0, 0}, {0, 1, 0, 0}, {0, 0, 1, 0}};
+        int nchain = p.chain >= 0 ? d->chains[p.chain].count : 0;
+        for(int k = 0; k < nchain; k++)
+        {
+            const float *m = d->xforms[d->chain_xf[d->chains[p.chain].first + k]].m;
+            double N[3][4];
+            for(int r = 0; r < 3; r++)
+                for(int c = 0; c < 4; c++)
+                {
+                    double v = c == 3 ? (double)m[4 * r + 3] : 0.0;
+                    for(int j = 0; j < 3; j++)
+                        v += (double)m[4 * r + j] * M[j][c];
+                    N[r][c] = v;
+                }
+            memcpy(M, N, sizeof(M));
+        }
+        uint32_t tag = prim << 1, tags = tag | (tag << 16);
+        if(p.type == PTB_PRIM_SPHERE)
+        {
+            uint32_t negR2 = f2u(-p.p[3]);
+            if(nchain == 0)
+            {
+                out.push_back(make_uint4(FK_SPHERE, tags, negR2, 0));
+                header = out.size() - 1;
+                out.push_back(make_uint4(f2u(-p.p[0]), f2u(-p.p[1]), f2u(-p.p[2]), 0));
+            }
+            else
+            {
+                out.push_back(make_uint4(FK_SPHERE_XF, tags, negR2, 0));
+                header = out.size() - 1;
+                for(int r = 0; r < 3; r++)
+                    out.push_back(make_uint4(f2u((float)M[r][0]), f2u((float)M[r][1]), f2u((float)M[r][2]), f2u((float)(M[r][3] - (double)p.p[r]))));
+            }
+        }
+        else
+        {
+            double n[3], D = p.p[3];
+            for(int j = 0; j < 3; j++)
+                n[j] = (double)p.p[0] * M[0][j] + (double)p.p[1] * M[1][j] + (double)p.p[2] * M[2][j];
+            D += (double)p.p[0] * M[0][3] + (double)p.p[1] * M[1][3] + (double)p.p[2] * M[2][3];
+            out.push_back(make_uint4(FK_PLANE, tags, 0, 0));
+            header = out.size() - 1;
+            out.push_back(make_uint4(f2u((float)n[0]), f2u((float)n[1]), f2u((float)n[2]), f2u((float)D)));
+        }
+        sealed = false;
+        freshLeaf = true;
+    }
+    out.push_back(make_uint4(FK_END, 0, 0, 0));
+}
+
 static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s)
 {
     if(!d || d->abi_version != PTB200_ABI_VERSION)
@@ -328,9 +446,13 @@ static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s)
     }
     if(sizes.size() != 1)
         return fail(PTB_EINVAL, "CSG program does not leave exactly one object on the stack");
+    if(maxStack > PTB_FAST_MAX_STACK)
+        return fail(PTB_EINVAL, "CSG tree needs more than 32 pending operands (right-deep nesting); rebalance it");
     if(poolBound > 65535)
         return fail(PTB_EINVAL, "scene too large for 16-bit span-pool offsets");
     prog.push_back(make_uint4(DK_END, 0, 0, 0));
+    std::vector<uint4> fast;
+    compileFastProgram(d, fast);
 
     std::vector<float4> geo(d->n_prims);
     std::vector<int4> meta(d->n_prims);
@@ -364,11 +486,12 @@ static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s)
     DevScene &dev = s->dev;
     memset(&dev, 0, sizeof(dev));
     int rc;
-    if((rc = upload(s, prog, &dev.program)) || (rc = upload(s, geo, &dev.primGeo)) || (rc = upload(s, meta, &dev.primMeta)) ||
+    if((rc = upload(s, prog, &dev.program)) || (rc = upload(s, fast, &dev.fastProgram)) || (rc = upload(s, geo, &dev.primGeo)) || (rc = upload(s, meta, &dev.primMeta)) ||
        (rc = upload(s, chainXf, &dev.chainXf)) || (rc = upload(s, xf, &dev.xforms)) || (rc = upload(s, mats, &dev.materials)) ||
        (rc = upload(s, texops, &dev.texops)) || (rc = upload(s, texdata, &dev.texdata)))
         return rc;
     dev.programWords = (int)prog.size();
+    dev.fastWords = (int)fast.size();
     dev.nPrims = d->n_prims, dev.nMaterials = d->n_materials, dev.nTexops = d->n_texops;
     dev.maxStack = maxStack, dev.poolBound = poolBound;
     for(int i = 0; i < d->n_images; i++)
@@ -450,15 +573,24 @@ static int chooseConfig(PtbScene *s, int which, DeviceBuffer &overflow, CsgConfi
 {
     const DevScene &dev = s->dev;
     cfg.threads = 128;
-    int cap = std::min(dev.poolBound, 16);
+    cfg.fast = which != 1;
+    int cap = std::min(dev.poolBound, cfg.fast ? 12 : 16);
     if(const char *e = getenv("PTB200_POOL_CAP"))
         cap = std::max(2, std::min(dev.poolBound, atoi(e)));
     cfg.cap = cap;
-    cfg.stageProgram = (size_t)dev.programWords * 16 <= 64 * 1024 ? 1 : 0;
-    cfg.smemBytes = csgSharedBytes(dev, cfg.threads, cfg.cap, cfg.stageProgram);
+    if(cfg.fast)
+    {
+        cfg.stageProgram = (size_t)dev.fastWords * 16 <= 96 * 1024 ? 1 : 0;
+        cfg.smemBytes = fastSharedBytes(dev, cfg.cap, cfg.stageProgram);
+    }
+    else
+    {
+        cfg.stageProgram = (size_t)dev.programWords * 16 <= 64 * 1024 ? 1 : 0;
+        cfg.smemBytes = csgSharedBytes(dev, cfg.threads, cfg.cap, cfg.stageProgram);
+    }
     if(cfg.smemBytes > s->smemOptin)
         return fail(PTB_EINVAL, "scene needs more shared memory per CTA than the device offers");
-    int perSm = csgBlocksPerSm(which, cfg.threads, cfg.smemBytes);
+    int perSm = csgBlocksPerSm(which, cfg.threads, cfg.smemBytes, !cfg.stageProgram);
     if(perSm <= 0)
         return fail(PTB_ECUDA, "kernel does not fit on an SM with this shared-memory size");
     if(const char *e = getenv("PTB200_BLOCKS_PER_SM"))
@@ -650,6 +782,12 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
     const int nPasses = (p->spp + perPass - 1) / perPass;
     const int stages = p->max_depth + 1; // primary + max_depth bounces
     CU(sx.queues.ensure(capacity * 64 * 2));
+    CU(sx.hits.ensure(capacity * sizeof(uint2)));
+    uint2 *hits = (uint2 *)sx.hits.p;
+    int shadePerSm = shadeBlocksPerSm();
+    if(shadePerSm <= 0)
+        return fail(PTB_ECUDA, "shade kernel does not fit on an SM");
+    const int shadeBlocks = shadePerSm * s->smCount;
     CU(sx.counters.ensure((size_t)nPasses * (stages + 1) * sizeof(unsigned)));
     CU(cudaMemsetAsync(sx.counters.p, 0, (size_t)nPasses * (stages + 1) * sizeof(unsigned), stream));
     RayQueue q[2];
@@ -682,14 +820,18 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
         pass.sampleBase = p->sample_offset + i * perPass * p->sample_stride;
         if(timed)
             CU(cudaEventRecord(sx.events[3 * i], stream));
-        launchPrimary(s->dev, cfg, pass, accum, q[0], c, stream);
+        launchTracePrimary(s->dev, cfg, pass, hits, stream);
+        launchShade(s->dev, shadeBlocks, true, pass, accum, hits, q[0], nullptr, q[0], c, stream);
         if(timed)
             CU(cudaEventRecord(sx.events[3 * i + 1], stream));
         for(int b = 1; b <= p->max_depth; b++)
-            launchBounce(s->dev, cfg, pass, accum, q[(b - 1) & 1], c + (b - 1), q[b & 1], c + b, stream);
+        {
+            launchTraceQueue(s->dev, cfg, q[(b - 1) & 1], c + (b - 1), hits, stream);
+            launchShade(s->dev, shadeBlocks, false, pass, accum, hits, q[(b - 1) & 1], c + (b - 1), q[b & 1], c + b, stream);
+        }
         if(timed)
             CU(cudaEventRecord(sx.events[3 * i + 2], stream));
-        launches += 1 + p->max_depth;
+        launches += 2 + 2 * (uint64_t)p->max_depth;
         CU(cudaGetLastError());
     }
     if(!timed)

@@ -164,13 +164,14 @@ __device__ __forceinline__ bool planeSpan(V3 o, V3 d, float4 g, float &t0, float
 
 // ---- merges ---------------------------------------------------------------------------------
 
+template <class P>
 struct MergeCursor
 {
-    const Pool &pool;
+    const P &pool;
     int a, aEnd, b, bEnd, out;
     SpanRec spanA, spanB;
     bool aEnded, bEnded;
-    __device__ __forceinline__ MergeCursor(const Pool &pool, int a0, int b0, int top, int dst) : pool(pool), a(a0), aEnd(b0), b(b0), bEnd(top), out(dst), aEnded(false), bEnded(false)
+    __device__ __forceinline__ MergeCursor(const P &pool, int a0, int b0, int top, int dst) : pool(pool), a(a0), aEnd(b0), b(b0), bEnd(top), out(dst), aEnded(false), bEnded(false)
     {
         spanA.t0 = spanA.t1 = spanB.t0 = spanB.t1 = 0.0f;
         spanA.tags = spanB.tags = 0u;
@@ -195,9 +196,10 @@ struct MergeCursor
 
 // Runs one combinator to exhaustion, writing its output spans from `dst` on; returns the slot
 // after the last output.
-static __device__ __noinline__ int mergeLists(const Pool &pool, int kind, int a0, int b0, int top, int dst)
+template <class P>
+static __device__ __forceinline__ int mergeListsT(const P &pool, int kind, int a0, int b0, int top, int dst)
 {
-    MergeCursor m(pool, a0, b0, top, dst);
+    MergeCursor<P> m(pool, a0, b0, top, dst);
     m.nextA();
     m.nextB();
     if(kind == DK_UNION)
@@ -324,6 +326,8 @@ static __device__ __noinline__ int mergeLists(const Pool &pool, int kind, int a0
     return m.out;
 }
 
+static __device__ __noinline__ int mergeLists(const Pool &pool, int kind, int a0, int b0, int top, int dst) { return mergeListsT(pool, kind, a0, b0, top, dst); }
+
 // ---- program evaluation ---------------------------------------------------------------------
 
 // Runs the whole program for one ray; on return the root span list is pool slots [0, return).
@@ -415,7 +419,8 @@ __device__ __forceinline__ int evalProgram(const uint4 *__restrict__ prog, const
 
 // First boundary with t >= eps: the scan of traceRay, reference include/path-trace.h:66-101.
 // Returns PTB_HIT_* (0 miss, 1 entered at a span start, 2 left at a span end).
-__device__ __forceinline__ int firstHit(const Pool &pool, int n, float &t, uint32_t &tag)
+template <class P>
+__device__ __forceinline__ int firstHit(const P &pool, int n, float &t, uint32_t &tag)
 {
     for(int i = 0; i < n; i++)
     {

@@ -1,0 +1,349 @@
+// ptb_csg_fast.cuh — the span-list CSG evaluator the renderer runs (fast arithmetic policy).
+//
+// Same algorithm and the same merge state machines as ptb_csg.cuh (the bit-exact evaluator),
+// re-laid-out for issue rate.  ncu on the generic evaluator (profiles/r01a_full_c4.txt): 12 100
+// warp instructions per ray on the 70-primitive scene, only 20 % of them FP32 arithmetic — the
+// rest was generic-address LD/ST, 64-bit address arithmetic, per-op dispatch and local memory.
+//
+// The host (ptb_capi.cu, compileFastProgram) turns the postfix program into a stream of
+// 16-byte words in which
+//   * every TransformedObject chain is pre-multiplied (in double) into ONE 3x4 matrix, and the
+//     sphere centre is folded into its translation:  oc = M o + (t - c)   (3 FFMA per row);
+//   * a transformed plane becomes a world-space plane: n' = M^T n, D' = D + n.t, so a plane
+//     costs 6 FFMA whatever wraps it;
+//   * the operator that follows a leaf rides in the leaf's header as its `action`, further
+//     operators as 2-bit codes: no fetch/dispatch per operator;
+//   * a SKIP word sits before the right operand of every Difference / Intersection: when no
+//     lane of the warp has a non-empty left operand the whole right subtree is jumped over
+//     ({} \ B = {} n B = {}: src/difference.cpp:88-89, src/intersection.cpp:88-90).
+//
+// EMPTY LISTS COST NOTHING.  Most leaves miss, so most lists on the operand stack are empty.
+// The stack is therefore one bit per entry (`bits`, bit 0 = top of stack: list non-empty?) and
+// only non-empty lists own pool slots and an entry on the start stack.  A u {} = A, A \ {} = A,
+// {} \ B = {}, A n {} = {} are then pure bit arithmetic — exactly what the reference's state
+// machines produce when aEnded / bEnded is set from the start (src/union.cpp:88-102,
+// src/difference.cpp:88-99, src/intersection.cpp:88-90) — and the real streaming merges
+// (mergeListsT, shared with the exact evaluator) only run for lanes where both lists have spans.
+// The tree shape, the merge rules and hence span topology are untouched; only float rounding
+// differs from the reference (|dt|/t ~ 1e-7, gate 1e-5).
+//
+// Shared memory is addressed with 32-bit shared-window addresses through ld.shared/st.shared
+// (no generic pointers, no per-access window-base recomputation).  Layout per CTA:
+//     [ program words ][ span pool: cap x {t0,t1,tags} x FT ][ start stack: depth x FT ]
+// Pool and stack are [slot][thread]: conflict-free for any mix of slots across a warp.
+#pragma once
+#include "ptb_csg.cuh"
+
+namespace ptb
+{
+
+extern __shared__ uint4 ptbSmem[];
+
+enum
+{
+    FK_END = 0,
+    FK_SPHERE_XF = 1, // header {x, tags, -r^2, 0}, 3 rows of the folded matrix
+    FK_PLANE = 2,     // header {x, tags, 0, 0}, float4 (n.xyz, D) in world space
+    FK_SPHERE = 3,    // header {x, tags, -r^2, 0}, float4 (-c.xyz, 0)
+    FK_OPS = 4,       // header only: operators that could not ride on the previous leaf
+    FK_SKIP = 5       // header only: x >> 4 = words to jump when the top list is empty warp-wide
+};
+// header.x = kind | action << 4 | nPost << 8 | post << 12 (up to 10 operators, 2 bits each, first lowest)
+enum
+{
+    FA_PUSH = 0, // no operator follows the leaf directly
+    FA_UNION = 1,
+    FA_DIFFERENCE = 2,
+    FA_INTERSECTION = 3
+};
+#define PTB_FAST_THREADS 128
+#define PTB_FAST_MAX_POST 10
+#define PTB_FAST_MAX_STACK 32
+
+__device__ __forceinline__ uint4 lds128(uint32_t a)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t a)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void sts128(uint32_t a, uint4 v) { asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory"); }
+
+// Span pool in shared memory with a global overflow area for slots >= cap.
+struct FastPool
+{
+    uint32_t base; // shared address of slot 0 for this thread
+    int cap;
+    float *ovf; // global overflow, already offset to this thread, or NULL
+    size_t ovfStride;
+
+    __device__ __forceinline__ SpanRec load(int slot) const
+    {
+        SpanRec r;
+        if(slot < cap)
+        {
+            uint32_t a = base + (uint32_t)slot * (12u * PTB_FAST_THREADS);
+            r.t0 = __uint_as_float(lds32(a));
+            r.t1 = __uint_as_float(lds32(a + 4u * PTB_FAST_THREADS));
+            r.tags = lds32(a + 8u * PTB_FAST_THREADS);
+        }
+        else
+        {
+            const float *p = ovf + (size_t)(slot - cap) * 3 * ovfStride;
+            r.t0 = p[0];
+            r.t1 = p[ovfStride];
+            r.tags = __float_as_uint(p[2 * ovfStride]);
+        }
+        return r;
+    }
+    __device__ __forceinline__ void store(int slot, const SpanRec &r) const
+    {
+        if(slot < cap)
+        {
+            uint32_t a = base + (uint32_t)slot * (12u * PTB_FAST_THREADS);
+            sts32(a, __float_as_uint(r.t0));
+            sts32(a + 4u * PTB_FAST_THREADS, __float_as_uint(r.t1));
+            sts32(a + 8u * PTB_FAST_THREADS, r.tags);
+        }
+        else
+        {
+            float *p = ovf + (size_t)(slot - cap) * 3 * ovfStride;
+            p[0] = r.t0;
+            p[ovfStride] = r.t1;
+            p[2 * ovfStride] = __uint_as_float(r.tags);
+        }
+    }
+};
+
+struct FastCtx
+{
+    uint32_t prog; // shared address of the first program word (unused with a global program)
+    uint32_t stk;  // shared address of this thread's start stack
+    FastPool pool;
+};
+
+__device__ __forceinline__ float rcpApprox(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float sqrtApprox(float x)
+{
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// Evaluator state of one ray.
+struct FastState
+{
+    uint32_t bits; // operand stack, one bit per entry, bit 0 = top: does the list have spans?
+    int top;       // pool slots in use
+    uint32_t sp;   // shared address one past the top of the start stack (non-empty lists only)
+};
+
+// Real merge of the two top NON-EMPTY lists A = [a0, b0), B = [b0, top); returns the new top.
+// One out-of-line copy of the three state machines, everything passed by value (registers).
+static __device__ __noinline__ int fastMerge(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t op, int a0, int b0, int top)
+{
+    FastPool pool;
+    pool.base = poolBase, pool.cap = cap, pool.ovf = ovf, pool.ovfStride = ovfStride;
+    const int kind = (int)op - FA_UNION + DK_UNION;
+    if(b0 - a0 == 1 && top - b0 == 1)
+        return mergeListsT(pool, kind, a0, b0, top, a0); // both inputs are in registers before the first output
+    int end = mergeListsT(pool, kind, a0, b0, top, top);
+    int n = end - top;
+    for(int i = 0; i < n; i++)
+        pool.store(a0 + i, pool.load(top + i));
+    return a0 + n;
+}
+
+// The slow paths are out of line and take / return everything by value (registers), so the
+// hot loop stays a few hundred contiguous instructions (instruction-cache resident).
+//
+// Operator on the two top entries (ab: bit 1 = A, bit 0 = B) for lanes that need pool work.
+// Returns {result bit, top, sp}.
+static __device__ __noinline__ uint3 fastOpSlow(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t op, uint32_t ab, int top, uint32_t sp)
+{
+    const uint32_t W = 4u * PTB_FAST_THREADS;
+    if(ab == 3u)
+    {
+        int b0 = (int)lds32(sp - W), a0 = (int)lds32(sp - 2u * W);
+        top = fastMerge(poolBase, cap, ovf, ovfStride, op, a0, b0, top);
+        if(top == a0) // the result has no spans: it gives up its start-stack entry too
+            return make_uint3(0u, (uint32_t)top, sp - 2u * W);
+        return make_uint3(1u, (uint32_t)top, sp - W);
+    }
+    // exactly one operand has spans and the operator throws them away
+    sp -= W;
+    return make_uint3(0u, lds32(sp), sp);
+}
+
+// One operator on the bit stack; pool work only where needed.
+__device__ __forceinline__ void fastOp(const FastPool &pool, uint32_t op, FastState &st)
+{
+    const uint32_t ab = st.bits & 3u;
+    bool work;
+    uint32_t res;
+    if(op == FA_UNION)
+        work = ab == 3u, res = ab != 0u;
+    else if(op == FA_DIFFERENCE)
+        work = (ab & 1u) != 0u, res = ab >> 1; // B has spans: real merge (ab == 3) or B discarded (ab == 1)
+    else
+        work = ab != 0u, res = 0u; // both: real merge; one: discarded
+    if(work)
+    {
+        uint3 r = fastOpSlow(pool.base, pool.cap, pool.ovf, pool.ovfStride, op, ab, st.top, st.sp);
+        res = r.x, st.top = (int)r.y, st.sp = r.z;
+    }
+    st.bits = ((st.bits >> 2) << 1) | res;
+}
+
+// A leaf that produced a span: push it, or combine it with the list below per `action`.
+// Returns {bits, top, sp}.
+static __device__ __noinline__ uint3 fastLeafHit(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t action, float t0, float t1, uint32_t tags,
+                                                 uint32_t bits, int top, uint32_t sp)
+{
+    const uint32_t W = 4u * PTB_FAST_THREADS;
+    FastPool pool;
+    pool.base = poolBase, pool.cap = cap, pool.ovf = ovf, pool.ovfStride = ovfStride;
+    SpanRec s;
+    s.t0 = t0, s.t1 = t1, s.tags = tags;
+    const bool aHas = bits & 1u;
+    if(action == FA_PUSH || (action == FA_UNION && !aHas))
+    {
+        sts32(sp, (uint32_t)top);
+        pool.store(top, s);
+        return make_uint3(action == FA_PUSH ? (bits << 1) | 1u : bits | 1u, (uint32_t)(top + 1), sp + W);
+    }
+    if(!aHas)
+        return make_uint3(bits, (uint32_t)top, sp); // {} \ B and {} n B stay empty; B is never stored
+    int a0 = (int)lds32(sp - W);
+    pool.store(top, s);
+    int ntop = fastMerge(poolBase, cap, ovf, ovfStride, action, a0, top, top + 1);
+    if(ntop == a0)
+        return make_uint3(bits & ~1u, (uint32_t)ntop, sp - W);
+    return make_uint3(bits, (uint32_t)ntop, sp);
+}
+
+// Runs the whole program for one ray, all 32 lanes of the warp together (SKIP words vote);
+// the root span list is pool slots [0, return).
+template <bool GP>
+__device__ __forceinline__ int evalFast(const FastCtx &c, const uint4 *__restrict__ gprog, V3 o, V3 d)
+{
+    const uint32_t W = 4u * PTB_FAST_THREADS;
+    FastState st;
+    st.bits = 0u, st.top = 0, st.sp = c.stk;
+    uint32_t pc = GP ? 0u : c.prog; // GP: word index; else shared byte address
+#define PTB_PROG(i) (GP ? __ldg(gprog + pc + (i)) : lds128(pc + 16u * (i)))
+#define PTB_ADVANCE(n) (pc += GP ? (uint32_t)(n) : 16u * (uint32_t)(n))
+    for(;;)
+    {
+        const uint4 h = PTB_PROG(0);
+        const uint32_t kind = h.x & 15u;
+        if(kind <= FK_SPHERE)
+        {
+            if(kind == FK_END)
+                break;
+            bool hit;
+            float t0, t1;
+            if(kind == FK_SPHERE_XF)
+            { // transform(m, ray) folded with `origin - centre`; src/sphere.cpp:33-43
+                const uint4 u0 = PTB_PROG(1), u1 = PTB_PROG(2), u2 = PTB_PROG(3);
+                PTB_ADVANCE(4);
+                const float m00 = __uint_as_float(u0.x), m01 = __uint_as_float(u0.y), m02 = __uint_as_float(u0.z), m03 = __uint_as_float(u0.w);
+                const float m10 = __uint_as_float(u1.x), m11 = __uint_as_float(u1.y), m12 = __uint_as_float(u1.z), m13 = __uint_as_float(u1.w);
+                const float m20 = __uint_as_float(u2.x), m21 = __uint_as_float(u2.y), m22 = __uint_as_float(u2.z), m23 = __uint_as_float(u2.w);
+                float ox = fmaf(o.x, m00, fmaf(o.y, m01, fmaf(o.z, m02, m03)));
+                float oy = fmaf(o.x, m10, fmaf(o.y, m11, fmaf(o.z, m12, m13)));
+                float oz = fmaf(o.x, m20, fmaf(o.y, m21, fmaf(o.z, m22, m23)));
+                float dx = fmaf(d.x, m00, fmaf(d.y, m01, d.z * m02));
+                float dy = fmaf(d.x, m10, fmaf(d.y, m11, d.z * m12));
+                float dz = fmaf(d.x, m20, fmaf(d.y, m21, d.z * m22));
+                float a = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+                float b = fmaf(ox, dx, fmaf(oy, dy, oz * dz));
+                float cc = fmaf(ox, ox, fmaf(oy, oy, fmaf(oz, oz, __uint_as_float(h.z))));
+                float disc = fmaf(b, b, -(a * cc));
+                hit = disc > PTB_EPS;
+                if(hit)
+                {
+                    float s = sqrtApprox(disc), ia = rcpApprox(a);
+                    t0 = (-b - s) * ia;
+                    t1 = (-b + s) * ia;
+                }
+            }
+            else if(kind == FK_PLANE)
+            { // PlaneSpanIterator::init, src/plane.cpp:35-63, on the world-space plane
+                const uint4 u0 = PTB_PROG(1);
+                PTB_ADVANCE(2);
+                float nx = __uint_as_float(u0.x), ny = __uint_as_float(u0.y), nz = __uint_as_float(u0.z);
+                float divisor = fmaf(d.x, nx, fmaf(d.y, ny, d.z * nz));
+                float numerator = -fmaf(o.x, nx, fmaf(o.y, ny, fmaf(o.z, nz, __uint_as_float(u0.w))));
+                float t = numerator * rcpApprox(divisor);
+                bool parallel = fabsf(divisor) < PTB_EPS * PTB_EPS || !(fabsf(t) < PTB_MAX_VALUE);
+                hit = !parallel || fabsf(numerator) < PTB_EPS * PTB_EPS;
+                bool lo = !parallel && divisor < 0.0f, hi = !parallel && !(divisor < 0.0f);
+                t0 = lo ? t : -PTB_MAX_VALUE;
+                t1 = hi ? t : PTB_MAX_VALUE;
+            }
+            else
+            {
+                const uint4 u0 = PTB_PROG(1);
+                PTB_ADVANCE(2);
+                float ox = o.x + __uint_as_float(u0.x), oy = o.y + __uint_as_float(u0.y), oz = o.z + __uint_as_float(u0.z);
+                float a = fmaf(d.x, d.x, fmaf(d.y, d.y, d.z * d.z));
+                float b = fmaf(ox, d.x, fmaf(oy, d.y, oz * d.z));
+                float cc = fmaf(ox, ox, fmaf(oy, oy, fmaf(oz, oz, __uint_as_float(h.z))));
+                float disc = fmaf(b, b, -(a * cc));
+                hit = disc > PTB_EPS;
+                if(hit)
+                {
+                    float s = sqrtApprox(disc), ia = rcpApprox(a);
+                    t0 = (-b - s) * ia;
+                    t1 = (-b + s) * ia;
+                }
+            }
+            const uint32_t action = (h.x >> 4) & 3u;
+            if(hit)
+            {
+                uint3 r = fastLeafHit(c.pool.base, c.pool.cap, c.pool.ovf, c.pool.ovfStride, action, t0, t1, h.y, st.bits, st.top, st.sp);
+                st.bits = r.x, st.top = (int)r.y, st.sp = r.z;
+            }
+            else if(action == FA_PUSH)
+                st.bits <<= 1;
+            else if(action == FA_INTERSECTION && (st.bits & 1u))
+            { // A n {} = {}: A's spans are dropped
+                st.sp -= W;
+                st.top = (int)lds32(st.sp);
+                st.bits &= ~1u;
+            }
+        }
+        else if(kind == FK_SKIP)
+        {
+            PTB_ADVANCE(1);
+            if(!__any_sync(0xFFFFFFFFu, st.bits & 1u))
+                PTB_ADVANCE(h.x >> 4);
+            continue;
+        }
+        else
+            PTB_ADVANCE(1);
+        uint32_t npost = (h.x >> 8) & 15u, post = h.x >> 12;
+        while(npost)
+        {
+            fastOp(c.pool, (post & 3u) + FA_UNION, st);
+            post >>= 2, npost--;
+        }
+    }
+#undef PTB_PROG
+#undef PTB_ADVANCE
+    return st.top;
+}
+
+} // namespace ptb

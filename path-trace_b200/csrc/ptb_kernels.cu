@@ -11,10 +11,16 @@
 // free [slot][thread] shared-memory pool; queue records are four float4 SoA streams written
 // through __ballot_sync/__popc warp-aggregated compaction so every store is coalesced.
 #include "ptb_launch.h"
+#include "ptb_csg_fast.cuh"
 #include "ptb_shade.cuh"
 
 namespace ptb
 {
+
+#define PTB_SHADE_THREADS 128
+#ifndef PTB_TRACE_MIN_CTAS
+#define PTB_TRACE_MIN_CTAS 8
+#endif
 
 // ---- shared memory carve-up -----------------------------------------------------------------
 size_t csgSharedBytes(const DevScene &sc, int threads, int cap, bool stageProgram)
@@ -22,6 +28,13 @@ size_t csgSharedBytes(const DevScene &sc, int threads, int cap, bool stageProgra
     size_t bytes = stageProgram ? (size_t)sc.programWords * 16 : 0;
     bytes += (size_t)cap * threads * 12;                 // t0, t1, tags
     bytes += (size_t)sc.maxStack * threads * 2;          // stack-entry start offsets (u16)
+    return (bytes + 15) & ~(size_t)15;
+}
+size_t fastSharedBytes(const DevScene &sc, int cap, bool stageProgram)
+{
+    size_t bytes = stageProgram ? (size_t)sc.fastWords * 16 : 0;
+    bytes += (size_t)cap * PTB_FAST_THREADS * 12;               // t0, t1, tags
+    bytes += (size_t)(sc.maxStack + 1) * PTB_FAST_THREADS * 4;  // list-start stack (u32)
     return (bytes + 15) & ~(size_t)15;
 }
 
@@ -59,14 +72,36 @@ __device__ __forceinline__ CsgShared setupCsg(const DevScene &sc, int cap, int s
     return s;
 }
 
-// Intersects one ray with the scene and resolves the first hit (normal, material, relative ior).
-template <bool EX>
-__device__ __forceinline__ int traceFirstHit(const DevScene &sc, const CsgShared &cs, V3 o, V3 d, Hit &hit, uint32_t &tag, int &nSpans)
+// Fast evaluator: stage the program (unless GP: it stays in global memory) and lay out pool + stack.
+template <bool GP>
+__device__ __forceinline__ FastCtx setupFast(const DevScene &sc, int cap, float *overflow, size_t ovfStride)
 {
-    nSpans = evalProgram<EX>(cs.program, cs.pool, o, d);
+    FastCtx c;
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(ptbSmem);
+    uint32_t words = 0;
+    if(!GP)
+    {
+        words = (uint32_t)sc.fastWords;
+        for(uint32_t i = threadIdx.x; i < words; i += PTB_FAST_THREADS)
+            sts128(base + 16u * i, __ldg(sc.fastProgram + i));
+    }
+    c.prog = base;
+    c.pool.base = base + 16u * words + 4u * threadIdx.x;
+    c.pool.cap = cap;
+    c.pool.ovf = overflow ? overflow + (size_t)blockIdx.x * PTB_FAST_THREADS + threadIdx.x : nullptr;
+    c.pool.ovfStride = ovfStride;
+    c.stk = c.pool.base + (uint32_t)cap * (12u * PTB_FAST_THREADS);
+    __syncthreads();
+    return c;
+}
+
+// Resolves the first boundary with t >= eps into normal, material and relative ior.
+template <bool EX, class P>
+__device__ __forceinline__ int resolveFirstHit(const DevScene &sc, const P &pool, int nSpans, V3 o, V3 d, Hit &hit, uint32_t &tag)
+{
     float t = -1.f;
     tag = 0u;
-    int kind = firstHit(cs.pool, nSpans, t, tag);
+    int kind = firstHit(pool, nSpans, t, tag);
     hit.t = t;
     if(kind == PTB_HIT_MISS)
         return kind;
@@ -86,11 +121,48 @@ __device__ __forceinline__ int traceFirstHit(const DevScene &sc, const CsgShared
     return kind;
 }
 
+template <bool EX, class P>
+__device__ __forceinline__ void writeHitAndSpans(const DevScene &sc, const P &pool, size_t i, int kind, int nSpans, const Hit &hit, uint32_t tag, V3 o, V3 d,
+                                                 PtbHit *__restrict__ hits, PtbSpan *__restrict__ spans, int maxSpans)
+{
+    float4 a, b;
+    if(kind == PTB_HIT_MISS)
+    {
+        a = make_float4(hit.t, 0.f, 0.f, 0.f);
+        b = make_float4(__int_as_float(kind), __int_as_float(-1), __int_as_float(-1), __int_as_float(nSpans));
+    }
+    else
+    {
+        a = make_float4(hit.t, hit.n.x, hit.n.y, hit.n.z);
+        b = make_float4(__int_as_float(kind), __int_as_float((int)(tag >> 1)), __int_as_float(hit.mat), __int_as_float(nSpans));
+    }
+    // 32-byte record as two float4 stores
+    float4 *dst = reinterpret_cast<float4 *>(hits + i);
+    dst[0] = a;
+    dst[1] = b;
+    if(spans)
+    {
+        int m = nSpans < maxSpans ? nSpans : maxSpans;
+        for(int s = 0; s < m; s++)
+        {
+            SpanRec r = pool.load(s);
+            PtbSpan &ps = spans[i * (size_t)maxSpans + s];
+            V3 sn = boundaryNormal<EX>(sc, startTag(r), r.t0, o, d);
+            V3 en = boundaryNormal<EX>(sc, endTag(r), r.t1, o, d);
+            ps.start = r.t0, ps.end = r.t1;
+            ps.start_normal[0] = sn.x, ps.start_normal[1] = sn.y, ps.start_normal[2] = sn.z;
+            ps.end_normal[0] = en.x, ps.end_normal[1] = en.y, ps.end_normal[2] = en.z;
+            ps.start_prim = (int)(startTag(r) >> 1), ps.end_prim = (int)(endTag(r) >> 1);
+            ps.start_material = __ldg(&sc.primMeta[ps.start_prim]).y;
+            ps.end_material = __ldg(&sc.primMeta[ps.end_prim]).y;
+        }
+    }
+}
+
 // ---- ray-batch intersection -------------------------------------------------------------------
-template <bool EX>
-__global__ void __launch_bounds__(128) intersectKernel(DevScene sc, int cap, int stageProgram, float *overflow, size_t ovfStride, const float4 *__restrict__ origins,
-                                                       const float4 *__restrict__ dirs, size_t n, PtbHit *__restrict__ hits, PtbSpan *__restrict__ spans,
-                                                       int maxSpans)
+// Exact policy: the generic evaluator, bit-identical to the reference.
+__global__ void __launch_bounds__(128) intersectExactKernel(DevScene sc, int cap, int stageProgram, float *overflow, size_t ovfStride, const float4 *__restrict__ origins,
+                                                            const float4 *__restrict__ dirs, size_t n, PtbHit *__restrict__ hits, PtbSpan *__restrict__ spans, int maxSpans)
 {
     CsgShared cs = setupCsg(sc, cap, stageProgram, overflow, ovfStride);
     size_t stride = (size_t)gridDim.x * blockDim.x;
@@ -100,43 +172,38 @@ __global__ void __launch_bounds__(128) intersectKernel(DevScene sc, int cap, int
         V3 o = mk(o4.x, o4.y, o4.z), d = mk(d4.x, d4.y, d4.z);
         Hit hit;
         uint32_t tag;
-        int nSpans;
-        int kind = traceFirstHit<EX>(sc, cs, o, d, hit, tag, nSpans);
-        PtbHit out;
-        out.t = hit.t;
-        out.kind = kind;
-        out.n_spans = nSpans;
-        if(kind == PTB_HIT_MISS)
+        int nSpans = evalProgram<true>(cs.program, cs.pool, o, d);
+        int kind = resolveFirstHit<true>(sc, cs.pool, nSpans, o, d, hit, tag);
+        writeHitAndSpans<true>(sc, cs.pool, i, kind, nSpans, hit, tag, o, d, hits, spans, maxSpans);
+    }
+}
+
+// Fast policy: the evaluator the renderer runs.
+template <bool GP>
+__global__ void __launch_bounds__(PTB_FAST_THREADS) intersectFastKernel(DevScene sc, int cap, float *overflow, size_t ovfStride, const float4 *__restrict__ origins,
+                                                                        const float4 *__restrict__ dirs, size_t n, PtbHit *__restrict__ hits, PtbSpan *__restrict__ spans,
+                                                                        int maxSpans)
+{
+    FastCtx cx = setupFast<GP>(sc, cap, overflow, ovfStride);
+    size_t stride = (size_t)gridDim.x * PTB_FAST_THREADS;
+    // warp-uniform trip count: the evaluator needs all 32 lanes (idle lanes carry a null ray)
+    for(size_t base = (size_t)blockIdx.x * PTB_FAST_THREADS + (threadIdx.x & ~31u); base < n; base += stride)
+    {
+        size_t i = base + (threadIdx.x & 31u);
+        bool valid = i < n;
+        V3 o = mk(0.f, 0.f, 0.f), d = o;
+        if(valid)
         {
-            out.normal[0] = out.normal[1] = out.normal[2] = 0.f;
-            out.prim = out.material = -1;
+            float4 o4 = __ldg(&origins[i]), d4 = __ldg(&dirs[i]);
+            o = mk(o4.x, o4.y, o4.z), d = mk(d4.x, d4.y, d4.z);
         }
-        else
+        int nSpans = evalFast<GP>(cx, sc.fastProgram, o, d);
+        if(valid)
         {
-            out.normal[0] = hit.n.x, out.normal[1] = hit.n.y, out.normal[2] = hit.n.z;
-            out.prim = (int)(tag >> 1);
-            out.material = hit.mat;
-        }
-        // 32-byte record as two float4 stores
-        float4 *dst = reinterpret_cast<float4 *>(hits + i);
-        dst[0] = make_float4(out.t, out.normal[0], out.normal[1], out.normal[2]);
-        dst[1] = make_float4(__int_as_float(out.kind), __int_as_float(out.prim), __int_as_float(out.material), __int_as_float(out.n_spans));
-        if(spans)
-        {
-            int m = nSpans < maxSpans ? nSpans : maxSpans;
-            for(int s = 0; s < m; s++)
-            {
-                SpanRec r = cs.pool.load(s);
-                PtbSpan &ps = spans[i * (size_t)maxSpans + s];
-                V3 sn = boundaryNormal<EX>(sc, startTag(r), r.t0, o, d);
-                V3 en = boundaryNormal<EX>(sc, endTag(r), r.t1, o, d);
-                ps.start = r.t0, ps.end = r.t1;
-                ps.start_normal[0] = sn.x, ps.start_normal[1] = sn.y, ps.start_normal[2] = sn.z;
-                ps.end_normal[0] = en.x, ps.end_normal[1] = en.y, ps.end_normal[2] = en.z;
-                ps.start_prim = (int)(startTag(r) >> 1), ps.end_prim = (int)(endTag(r) >> 1);
-                ps.start_material = __ldg(&sc.primMeta[ps.start_prim]).y;
-                ps.end_material = __ldg(&sc.primMeta[ps.end_prim]).y;
-            }
+            Hit hit;
+            uint32_t tag;
+            int kind = resolveFirstHit<false>(sc, cx.pool, nSpans, o, d, hit, tag);
+            writeHitAndSpans<false>(sc, cx.pool, i, kind, nSpans, hit, tag, o, d, hits, spans, maxSpans);
         }
     }
 }
@@ -146,22 +213,32 @@ void launchIntersect(const DevScene &sc, const CsgConfig &cfg, const float4 *ori
 {
     if(exact)
     {
-        cudaFuncSetAttribute(intersectKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
-        intersectKernel<true><<<cfg.blocks, cfg.threads, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.stageProgram, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans,
-                                                                                  maxSpans);
+        cudaFuncSetAttribute(intersectExactKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        intersectExactKernel<<<cfg.blocks, cfg.threads, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.stageProgram, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans, maxSpans);
+    }
+    else if(cfg.stageProgram)
+    {
+        cudaFuncSetAttribute(intersectFastKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        intersectFastKernel<false><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans, maxSpans);
     }
     else
     {
-        cudaFuncSetAttribute(intersectKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
-        intersectKernel<false><<<cfg.blocks, cfg.threads, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.stageProgram, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans,
-                                                                                   maxSpans);
+        cudaFuncSetAttribute(intersectFastKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        intersectFastKernel<true><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans, maxSpans);
     }
 }
 
 // ---- wavefront render stages --------------------------------------------------------------------
+// One wavefront level = a TRACE kernel (rays -> first hit, 8 B per ray) and a SHADE kernel (hit ->
+// radiance + next ray).  They are separate kernels on purpose: fused, the shading state (path
+// throughput, RNG, texture interpreter) pushed the CSG loop to 94 registers / 5 CTAs per SM and
+// ptxas spilled inside the loop when capped at 64 (profiles/r01c_full_c4.txt); alone, the trace
+// kernel carries a ray and three words of evaluator state.
+//
 // Queue record (64 B, four coalesced float4 streams):
 //   q0 = origin.xyz, pixel        q1 = dir.xyz, strength
 //   q2 = throughput.rgb, sample   q3 = depth, rng block, -, -
+// Hit record (8 B): t, kind << 16 | boundary tag.
 __device__ __forceinline__ void queueStore(const RayQueue &q, unsigned idx, const PathState &ps)
 {
     q.q0[idx] = make_float4(ps.o.x, ps.o.y, ps.o.z, __uint_as_float(ps.pixel));
@@ -178,6 +255,91 @@ __device__ __forceinline__ void queueLoad(const RayQueue &q, unsigned idx, PathS
     ps.depth = __float_as_uint(e.x), ps.rngBlock = __float_as_uint(e.y);
 }
 
+// Camera sample i of this pass: pixel, global sample index, jittered pinhole ray
+// (tracePixel, reference include/path-trace.h:191-196).  Called by the primary trace kernel and
+// again by the primary shade kernel (regenerating is cheaper than a 64-byte round trip to HBM).
+__device__ __forceinline__ void cameraSample(const RenderPass &pass, unsigned nPix, unsigned long long i, PathState &ps)
+{
+    unsigned s = (unsigned)(i / nPix), p = (unsigned)(i % nPix);
+    int px = pass.x0 + (int)(p % (unsigned)pass.rw), py = pass.y0 + (int)(p / (unsigned)pass.rw);
+    ps.pixel = (unsigned)py * (unsigned)pass.width + (unsigned)px;
+    ps.sample = (unsigned)(pass.sampleBase + (int)s * pass.sampleStride);
+    Philox rng;
+    rngInit(rng, pass.seed, ps.pixel, ps.sample, 0u);
+    uint4 u = rngNext4(rng);
+    ps.rngBlock = rng.block;
+    float x = 2.f * ((float)px + u01(u.x)) / (float)pass.width - 1.f;
+    float y = 1.f - 2.f * ((float)py + u01(u.y)) / (float)pass.height;
+    ps.o = mk(0.f, 0.f, 0.f);
+    ps.d = mk(x * pass.sw, y * pass.sh, -pass.sd);
+    ps.thr = mk(1.f, 1.f, 1.f);
+    ps.strength = 1.f;
+    ps.depth = (unsigned)pass.maxDepth;
+}
+
+// Evaluates the CSG program for one ray per lane (all 32 lanes take part: SKIP words vote) and
+// packs the first boundary with t >= eps.
+template <bool GP>
+__device__ __forceinline__ uint2 traceOne(const DevScene &sc, const FastCtx &cx, V3 o, V3 d)
+{
+    int nSpans = evalFast<GP>(cx, sc.fastProgram, o, d);
+    float t = -1.f;
+    uint32_t tag = 0u;
+    int kind = firstHit(cx.pool, nSpans, t, tag);
+    return make_uint2(__float_as_uint(t), ((uint32_t)kind << 16) | tag);
+}
+
+template <bool GP>
+__global__ void __launch_bounds__(PTB_FAST_THREADS, PTB_TRACE_MIN_CTAS) tracePrimaryKernel(DevScene sc, int cap, float *overflow, size_t ovfStride, RenderPass pass,
+                                                                                           uint2 *__restrict__ hits)
+{
+    FastCtx cx = setupFast<GP>(sc, cap, overflow, ovfStride);
+    const unsigned nPix = (unsigned)pass.rw * (unsigned)pass.rh;
+    const unsigned long long total = (unsigned long long)nPix * (unsigned)pass.samplesThisPass;
+    const unsigned long long stride = (unsigned long long)gridDim.x * PTB_FAST_THREADS;
+    // warp-uniform trip count; idle lanes of the last warp carry a null ray
+    for(unsigned long long base = (unsigned long long)blockIdx.x * PTB_FAST_THREADS + (threadIdx.x & ~31u); base < total; base += stride)
+    {
+        unsigned long long i = base + (threadIdx.x & 31u);
+        bool valid = i < total;
+        V3 o = mk(0.f, 0.f, 0.f), d = o;
+        if(valid)
+        {
+            PathState ps;
+            cameraSample(pass, nPix, i, ps);
+            d = ps.d;
+        }
+        uint2 h = traceOne<GP>(sc, cx, o, d);
+        if(valid)
+            __stcs(&hits[i], h);
+    }
+}
+
+template <bool GP>
+__global__ void __launch_bounds__(PTB_FAST_THREADS, PTB_TRACE_MIN_CTAS) traceQueueKernel(DevScene sc, int cap, float *overflow, size_t ovfStride, RayQueue in,
+                                                                                         const unsigned *__restrict__ inCount, uint2 *__restrict__ hits)
+{
+    const unsigned total = *inCount;
+    if(total == 0u)
+        return;
+    FastCtx cx = setupFast<GP>(sc, cap, overflow, ovfStride);
+    const unsigned long long stride = (unsigned long long)gridDim.x * PTB_FAST_THREADS;
+    for(unsigned long long base = (unsigned long long)blockIdx.x * PTB_FAST_THREADS + (threadIdx.x & ~31u); base < total; base += stride)
+    {
+        unsigned long long i = base + (threadIdx.x & 31u);
+        bool valid = i < total;
+        V3 o = mk(0.f, 0.f, 0.f), d = o;
+        if(valid)
+        {
+            float4 a = __ldg(&in.q0[i]), b = __ldg(&in.q1[i]);
+            o = mk(a.x, a.y, a.z), d = mk(b.x, b.y, b.z);
+        }
+        uint2 h = traceOne<GP>(sc, cx, o, d);
+        if(valid)
+            __stcs(&hits[i], h);
+    }
+}
+
 // Framebuffer accumulation: one 16-byte vector reduction per contribution.  rgb = radiance sum,
 // a = completed camera samples (so a progressive reader can divide at any time).
 __device__ __forceinline__ void accumulate(float4 *accum, uint32_t pixel, V3 rad, float done)
@@ -186,109 +348,107 @@ __device__ __forceinline__ void accumulate(float4 *accum, uint32_t pixel, V3 rad
         atomicAdd(&accum[pixel], make_float4(rad.x, rad.y, rad.z, done));
 }
 
-// One wavefront step for the path in `ps` (valid lanes only): intersect, shade, accumulate;
-// then the warp compacts its surviving lanes into the out queue.
-__device__ __forceinline__ void traceShadeEnqueue(const DevScene &sc, const CsgShared &cs, bool valid, PathState &ps, uint64_t seed, uint32_t flags, float4 *accum,
-                                                  const RayQueue &out, unsigned *outCount)
+// Shade stage of one wavefront level: hit record -> normal, material, emitted radiance, next ray.
+// PRIMARY: path state is regenerated from the sample index; otherwise it is read from `in`.
+// Survivors are appended to `out` with __ballot_sync/__popc warp aggregation (one atomic per warp,
+// coalesced stores).
+template <bool PRIMARY>
+__global__ void __launch_bounds__(PTB_SHADE_THREADS) shadeKernel(DevScene sc, RenderPass pass, float4 *accum, const uint2 *__restrict__ hits, RayQueue in,
+                                                                 const unsigned *__restrict__ inCount, RayQueue out, unsigned *outCount)
 {
-    bool alive = false;
-    if(valid)
-    {
-        Hit hit;
-        uint32_t tag;
-        int nSpans;
-        int kind = traceFirstHit<false>(sc, cs, ps.o, ps.d, hit, tag, nSpans);
-        V3 rad = mk(0.f, 0.f, 0.f);
-        if(kind != PTB_HIT_MISS)
-        {
-            Philox rng;
-            rngInit(rng, seed, ps.pixel, ps.sample, ps.rngBlock);
-            alive = shadeVertex(sc, ps, hit, rng, flags, rad);
-            ps.rngBlock = rng.block;
-        }
-        accumulate(accum, ps.pixel, rad, alive ? 0.f : 1.f);
-    }
-    unsigned mask = __ballot_sync(0xFFFFFFFFu, alive);
-    if(mask)
-    {
-        unsigned lane = threadIdx.x & 31u;
-        int leader = __ffs(mask) - 1;
-        unsigned base = 0;
-        if((int)lane == leader)
-            base = atomicAdd(outCount, (unsigned)__popc(mask));
-        base = __shfl_sync(0xFFFFFFFFu, base, leader);
-        if(alive)
-            queueStore(out, base + __popc(mask & ((1u << lane) - 1u)), ps);
-    }
-}
-
-__global__ void __launch_bounds__(128) primaryKernel(DevScene sc, int cap, int stageProgram, float *overflow, size_t ovfStride, RenderPass pass, float4 *accum,
-                                                     RayQueue out, unsigned *outCount)
-{
-    CsgShared cs = setupCsg(sc, cap, stageProgram, overflow, ovfStride);
     const unsigned nPix = (unsigned)pass.rw * (unsigned)pass.rh;
-    const unsigned long long total = (unsigned long long)nPix * (unsigned)pass.samplesThisPass;
-    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    // warp-uniform trip count: every lane of a warp iterates together so the ballot is full
-    unsigned long long first = (unsigned long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31u);
-    for(unsigned long long base = first; base < total; base += stride)
+    const unsigned long long total = PRIMARY ? (unsigned long long)nPix * (unsigned)pass.samplesThisPass : (unsigned long long)*inCount;
+    const unsigned long long stride = (unsigned long long)gridDim.x * PTB_SHADE_THREADS;
+    for(unsigned long long base = (unsigned long long)blockIdx.x * PTB_SHADE_THREADS + (threadIdx.x & ~31u); base < total; base += stride)
     {
         unsigned long long i = base + (threadIdx.x & 31u);
-        bool valid = i < total;
+        bool alive = false;
         PathState ps;
-        if(valid)
+        if(i < total)
         {
-            unsigned s = (unsigned)(i / nPix), p = (unsigned)(i % nPix);
-            int px = pass.x0 + (int)(p % (unsigned)pass.rw), py = pass.y0 + (int)(p / (unsigned)pass.rw);
-            ps.pixel = (unsigned)py * (unsigned)pass.width + (unsigned)px;
-            ps.sample = (unsigned)(pass.sampleBase + (int)s * pass.sampleStride);
-            Philox rng;
-            rngInit(rng, pass.seed, ps.pixel, ps.sample, 0u);
-            uint4 u = rngNext4(rng);
-            ps.rngBlock = rng.block;
-            // tracePixel with per-sample jitter, reference include/path-trace.h:191-196
-            float x = 2.f * ((float)px + u01(u.x)) / (float)pass.width - 1.f;
-            float y = 1.f - 2.f * ((float)py + u01(u.y)) / (float)pass.height;
-            ps.o = mk(0.f, 0.f, 0.f);
-            ps.d = mk(x * pass.sw, y * pass.sh, -pass.sd);
-            ps.thr = mk(1.f, 1.f, 1.f);
-            ps.strength = 1.f;
-            ps.depth = (unsigned)pass.maxDepth;
+            uint2 h = __ldcs(&hits[i]);
+            if(PRIMARY)
+                cameraSample(pass, nPix, i, ps);
+            else
+                queueLoad(in, (unsigned)i, ps);
+            int kind = (int)(h.y >> 16);
+            V3 rad = mk(0.f, 0.f, 0.f);
+            if(kind != PTB_HIT_MISS)
+            {
+                uint32_t tag = h.y & 0xFFFFu;
+                Hit hit;
+                hit.t = __uint_as_float(h.x);
+                V3 n = boundaryNormal<false>(sc, tag, hit.t, ps.o, ps.d);
+                hit.mat = __ldg(&sc.primMeta[tag >> 1]).y;
+                if(kind == PTB_HIT_ENTER)
+                    hit.n = n, hit.ior = sc.materials[hit.mat].iorIn; // path-trace.h:72-81
+                else
+                    hit.n = neg(n), hit.ior = sc.materials[hit.mat].ior; // path-trace.h:86-95
+                Philox rng;
+                rngInit(rng, pass.seed, ps.pixel, ps.sample, ps.rngBlock);
+                alive = shadeVertex(sc, ps, hit, rng, pass.flags, rad);
+                ps.rngBlock = rng.block;
+            }
+            accumulate(accum, ps.pixel, rad, alive ? 0.f : 1.f);
         }
-        traceShadeEnqueue(sc, cs, valid, ps, pass.seed, pass.flags, accum, out, outCount);
+        unsigned mask = __ballot_sync(0xFFFFFFFFu, alive);
+        if(mask)
+        {
+            unsigned lane = threadIdx.x & 31u;
+            int leader = __ffs(mask) - 1;
+            unsigned slot = 0;
+            if((int)lane == leader)
+                slot = atomicAdd(outCount, (unsigned)__popc(mask));
+            slot = __shfl_sync(0xFFFFFFFFu, slot, leader);
+            if(alive)
+                queueStore(out, slot + __popc(mask & ((1u << lane) - 1u)), ps);
+        }
     }
 }
 
-__global__ void __launch_bounds__(128) bounceKernel(DevScene sc, int cap, int stageProgram, float *overflow, size_t ovfStride, RenderPass pass, float4 *accum,
-                                                    RayQueue in, const unsigned *__restrict__ inCount, RayQueue out, unsigned *outCount)
+void launchTracePrimary(const DevScene &sc, const CsgConfig &cfg, const RenderPass &pass, uint2 *hits, cudaStream_t stream)
 {
-    const unsigned total = *inCount;
-    if(total == 0u)
-        return;
-    CsgShared cs = setupCsg(sc, cap, stageProgram, overflow, ovfStride);
-    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    unsigned long long first = (unsigned long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31u);
-    for(unsigned long long base = first; base < total; base += stride)
+    if(cfg.stageProgram)
     {
-        unsigned long long i = base + (threadIdx.x & 31u);
-        bool valid = i < total;
-        PathState ps;
-        if(valid)
-            queueLoad(in, (unsigned)i, ps);
-        traceShadeEnqueue(sc, cs, valid, ps, pass.seed, pass.flags, accum, out, outCount);
+        cudaFuncSetAttribute(tracePrimaryKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        tracePrimaryKernel<false><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, pass, hits);
+    }
+    else
+    {
+        cudaFuncSetAttribute(tracePrimaryKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        tracePrimaryKernel<true><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, pass, hits);
     }
 }
-
-void launchPrimary(const DevScene &sc, const CsgConfig &cfg, const RenderPass &pass, float4 *accum, RayQueue out, unsigned *outCount, cudaStream_t stream)
+void launchTraceQueue(const DevScene &sc, const CsgConfig &cfg, RayQueue in, const unsigned *inCount, uint2 *hits, cudaStream_t stream)
 {
-    cudaFuncSetAttribute(primaryKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
-    primaryKernel<<<cfg.blocks, cfg.threads, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.stageProgram, cfg.overflow, cfg.ovfStride, pass, accum, out, outCount);
+    if(cfg.stageProgram)
+    {
+        cudaFuncSetAttribute(traceQueueKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        traceQueueKernel<false><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, in, inCount, hits);
+    }
+    else
+    {
+        cudaFuncSetAttribute(traceQueueKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        traceQueueKernel<true><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, in, inCount, hits);
+    }
 }
-void launchBounce(const DevScene &sc, const CsgConfig &cfg, const RenderPass &pass, float4 *accum, RayQueue in, const unsigned *inCount, RayQueue out,
-                  unsigned *outCount, cudaStream_t stream)
+void launchShade(const DevScene &sc, int blocks, bool primary, const RenderPass &pass, float4 *accum, const uint2 *hits, RayQueue in, const unsigned *inCount, RayQueue out,
+                 unsigned *outCount, cudaStream_t stream)
 {
-    cudaFuncSetAttribute(bounceKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
-    bounceKernel<<<cfg.blocks, cfg.threads, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.stageProgram, cfg.overflow, cfg.ovfStride, pass, accum, in, inCount, out, outCount);
+    if(primary)
+        shadeKernel<true><<<blocks, PTB_SHADE_THREADS, 0, stream>>>(sc, pass, accum, hits, in, inCount, out, outCount);
+    else
+        shadeKernel<false><<<blocks, PTB_SHADE_THREADS, 0, stream>>>(sc, pass, accum, hits, in, inCount, out, outCount);
+}
+int shadeBlocksPerSm()
+{
+    int n = 0;
+    if(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<false>, PTB_SHADE_THREADS, 0) != cudaSuccess)
+    {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
 }
 
 // ---- resolve ------------------------------------------------------------------------------------
@@ -391,30 +551,24 @@ double launchFmaPeak(int blocks, int threads, int iters, cudaStream_t stream)
 namespace ptb
 {
 // Resident CTAs per SM for a CSG kernel at this shared-memory size (occupancy API).
-int csgBlocksPerSm(int which, int threads, size_t smemBytes)
+template <class K>
+static int occupancyOf(K kernel, int threads, size_t smemBytes)
 {
     int n = 0;
-    cudaError_t e;
-    if(which == 0)
-    {
-        cudaFuncSetAttribute(intersectKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, intersectKernel<false>, threads, smemBytes);
-    }
-    else if(which == 1)
-    {
-        cudaFuncSetAttribute(intersectKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, intersectKernel<true>, threads, smemBytes);
-    }
-    else
-    {
-        cudaFuncSetAttribute(primaryKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, primaryKernel, threads, smemBytes);
-    }
-    if(e != cudaSuccess)
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    if(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, smemBytes) != cudaSuccess)
     {
         cudaGetLastError();
         return 0;
     }
     return n;
+}
+int csgBlocksPerSm(int which, int threads, size_t smemBytes, bool globalProgram)
+{
+    if(which == 1)
+        return occupancyOf(intersectExactKernel, threads, smemBytes);
+    if(which == 0)
+        return globalProgram ? occupancyOf(intersectFastKernel<true>, threads, smemBytes) : occupancyOf(intersectFastKernel<false>, threads, smemBytes);
+    return globalProgram ? occupancyOf(tracePrimaryKernel<true>, threads, smemBytes) : occupancyOf(tracePrimaryKernel<false>, threads, smemBytes);
 }
 } // namespace ptb

@@ -16,6 +16,7 @@ struct CsgConfig
     int blocks;        // grid size (persistent: a multiple of the SM count)
     int cap;           // span-pool slots per thread kept in shared memory
     int stageProgram;  // 1: copy the program stream into shared memory first
+    int fast;          // 1: laid out for the fast evaluator (ptb_csg_fast.cuh), 128 threads
     size_t smemBytes;  // dynamic shared memory per block
     float *overflow;   // global spill area or NULL when cap >= scene.poolBound
     size_t ovfStride;  // = blocks * threads
@@ -42,23 +43,28 @@ struct RenderPass
 
 void launchIntersect(const DevScene &sc, const CsgConfig &cfg, const float4 *origins, const float4 *dirs, size_t n, PtbHit *hits, PtbSpan *spans, int maxSpans,
                      bool exact, cudaStream_t stream);
-// Primary wavefront stage: raygen + intersect + shade for rw*rh*samplesThisPass camera samples;
-// survivors are appended to `out`, *outCount counts them.
-void launchPrimary(const DevScene &sc, const CsgConfig &cfg, const RenderPass &pass, float4 *accum, RayQueue out, unsigned *outCount, cudaStream_t stream);
-// Bounce stage: *inCount rays from `in` -> intersect + shade -> survivors appended to `out`.
-void launchBounce(const DevScene &sc, const CsgConfig &cfg, const RenderPass &pass, float4 *accum, RayQueue in, const unsigned *inCount, RayQueue out,
-                  unsigned *outCount, cudaStream_t stream);
+// Trace stage of the first wavefront level: camera rays for rw*rh*samplesThisPass samples -> hits[i].
+void launchTracePrimary(const DevScene &sc, const CsgConfig &cfg, const RenderPass &pass, uint2 *hits, cudaStream_t stream);
+// Trace stage of a bounce level: *inCount rays of `in` -> hits[i].
+void launchTraceQueue(const DevScene &sc, const CsgConfig &cfg, RayQueue in, const unsigned *inCount, uint2 *hits, cudaStream_t stream);
+// Shade stage: hits -> accumulate + survivors appended to `out` (*outCount counts them).  primary:
+// path state regenerated from the sample index; else read from `in` (*inCount entries).
+void launchShade(const DevScene &sc, int blocks, bool primary, const RenderPass &pass, float4 *accum, const uint2 *hits, RayQueue in, const unsigned *inCount, RayQueue out,
+                 unsigned *outCount, cudaStream_t stream);
+int shadeBlocksPerSm();
 void launchResolve(const float4 *accum, float4 *rgba, size_t nPixels, cudaStream_t stream);
 void launchTextureEval(const DevScene &sc, int root, const float *pos, size_t n, float *rgb, float *f, uint32_t flags, cudaStream_t stream);
 void launchScatterSample(const float *normal, const float *refl, float scatter, size_t n, uint64_t seed, uint32_t flags, float *dirs, cudaStream_t stream);
 // FMA-chain microbenchmark: returns lane-FMAs executed.
 double launchFmaPeak(int blocks, int threads, int iters, cudaStream_t stream);
 size_t csgSharedBytes(const DevScene &sc, int threads, int cap, bool stageProgram);
+size_t fastSharedBytes(const DevScene &sc, int cap, bool stageProgram);
 
 } // namespace ptb
 
 namespace ptb
 {
-// which: 0 = intersect (fast), 1 = intersect (exact), 2 = render stages
-int csgBlocksPerSm(int which, int threads, size_t smemBytes);
+// which: 0 = intersect (fast), 1 = intersect (exact), 2 = render stages; globalProgram: the
+// program stream is too large for shared memory and is read through the read-only cache
+int csgBlocksPerSm(int which, int threads, size_t smemBytes, bool globalProgram);
 }

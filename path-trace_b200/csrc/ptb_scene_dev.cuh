@@ -34,6 +34,8 @@ struct DevScene
     const float *texdata;
     const DevImage *images;
     int nPrims, nMaterials, nTexops, nImages;
+    const uint4 *fastProgram; // the same program compiled for the fast evaluator (ptb_csg_fast.cuh)
+    int fastWords;
     int maxStack;             // deepest list stack the program reaches
     int poolBound;            // worst-case pool slots (incl. merge scratch)
 };
