@@ -161,8 +161,11 @@ enum {
                                rsqrt-based normalisation (|rel err| < 1e-6, within the 1e-5 gate). */
     PTB_FLAG_BILINEAR = 2u, /* non-reference extra: bilinear image fetch instead of the reference's
                                nearest texel                                        */
-    PTB_FLAG_REJECTION = 4u /* scatter by the reference's literal rejection loops
+    PTB_FLAG_REJECTION = 4u,/* scatter by the reference's literal rejection loops
                                (path-trace.h:142-158) instead of the divergence-free cap sampler   */
+    PTB_FLAG_ORIGIN0 = 8u   /* ptb200_intersect*: the caller promises every origin is (0,0,0), as for
+                               all camera rays (path-trace.h:196); selects the camera-ray variant of
+                               the fast evaluator, which the renderer's primary stage runs          */
 };
 
 /* ---- rendering ------------------------------------------------------------------------------ */

@@ -266,7 +266,11 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out)
         {
             uint32_t code = kind == PTB_OP_UNION ? 0u : kind == PTB_OP_DIFFERENCE ? 1u : 2u;
             if(freshLeaf && !sealed)
-                out[header].x |= (code + FA_UNION) << 4; // the leaf's action
+            {
+                out[header].x = (out[header].x & ~FH_MISS_SHIFT) | ((code + FA_UNION) << 4); // the leaf's action
+                if(code == 2u)
+                    out[header].x |= FH_TAIL; // a missed leaf under Intersection drops the list below
+            }
             else
             {
                 uint32_t n = sealed ? PTB_FAST_MAX_POST : (out[header].x >> 8) & 15u;
@@ -278,13 +282,13 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out)
                     n = 0;
                 }
                 out[header].x |= code << (12 + 2 * n);
-                out[header].x = (out[header].x & ~0xF00u) | ((n + 1) << 8);
+                out[header].x = (out[header].x & ~0xF00u) | ((n + 1) << 8) | FH_TAIL;
             }
             freshLeaf = false;
             if(kind != PTB_OP_UNION)
             { // the right operand ends here: close the skipped region
                 size_t w = skipWord[i];
-                out[w].x = FK_SKIP | (uint32_t)((out.size() - (w + 1)) << 4);
+                out[w].y = (uint32_t)(out.size() - (w + 1));
                 sealed = true;
             }
             continue;
@@ -319,13 +323,17 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out)
             uint32_t negR2 = f2u(-p.p[3]);
             if(nchain == 0)
             {
-                out.push_back(make_uint4(FK_SPHERE, tags, negR2, 0));
+                double c0 = (double)p.p[0] * p.p[0] + (double)p.p[1] * p.p[1] + (double)p.p[2] * p.p[2] - (double)p.p[3];
+                out.push_back(make_uint4(FK_SPHERE | FH_MISS_SHIFT, tags, negR2, f2u((float)c0)));
                 header = out.size() - 1;
                 out.push_back(make_uint4(f2u(-p.p[0]), f2u(-p.p[1]), f2u(-p.p[2]), 0));
             }
             else
             {
-                out.push_back(make_uint4(FK_SPHERE_XF, tags, negR2, 0));
+                double c0 = -(double)p.p[3];
+                for(int r = 0; r < 3; r++)
+                    c0 += (M[r][3] - (double)p.p[r]) * (M[r][3] - (double)p.p[r]);
+                out.push_back(make_uint4(FK_SPHERE_XF | FH_MISS_SHIFT, tags, negR2, f2u((float)c0)));
                 header = out.size() - 1;
                 for(int r = 0; r < 3; r++)
                     out.push_back(make_uint4(f2u((float)M[r][0]), f2u((float)M[r][1]), f2u((float)M[r][2]), f2u((float)(M[r][3] - (double)p.p[r]))));
@@ -337,7 +345,7 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out)
             for(int j = 0; j < 3; j++)
                 n[j] = (double)p.p[0] * M[0][j] + (double)p.p[1] * M[1][j] + (double)p.p[2] * M[2][j];
             D += (double)p.p[0] * M[0][3] + (double)p.p[1] * M[1][3] + (double)p.p[2] * M[2][3];
-            out.push_back(make_uint4(FK_PLANE, tags, 0, 0));
+            out.push_back(make_uint4(FK_PLANE | FH_MISS_SHIFT, tags, 0, 0));
             header = out.size() - 1;
             out.push_back(make_uint4(f2u((float)n[0]), f2u((float)n[1]), f2u((float)n[2]), f2u((float)D)));
         }
@@ -345,6 +353,30 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out)
         freshLeaf = true;
     }
     out.push_back(make_uint4(FK_END, 0, 0, 0));
+    // flag union-only tails, then pairs of consecutive transformed spheres (see ptb_csg_fast.cuh)
+    auto recordLength = [&](size_t w) { return (out[w].x & FK_SPHERE_XF) ? 4u : (out[w].x & (FK_PLANE | FK_SPHERE)) ? 2u : 1u; };
+    for(size_t w = 0; w < out.size(); w += recordLength(w))
+    {
+        uint32_t x = out[w].x, n = (x >> 8) & 15u;
+        if(!(x & FH_TAIL) || n == 0)
+            continue;
+        bool allUnion = (x & FK_CONTROL) || ((x >> 4) & 3u) != FA_INTERSECTION;
+        for(uint32_t k = 0; k < n; k++)
+            if((x >> (12 + 2 * k)) & 3u)
+                allUnion = false;
+        if(allUnion)
+            out[w].x |= FH_UNION_TAIL;
+    }
+    for(size_t w = 0; w < out.size();)
+    {
+        if((out[w].x & FK_SPHERE_XF) && !(out[w].x & FH_TAIL) && w + 4 < out.size() && (out[w + 4].x & FK_SPHERE_XF))
+        {
+            out[w].x |= FH_PAIR;
+            w += 8;
+        }
+        else
+            w += recordLength(w);
+    }
 }
 
 static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s)
@@ -574,6 +606,7 @@ static int chooseConfig(PtbScene *s, int which, DeviceBuffer &overflow, CsgConfi
     const DevScene &dev = s->dev;
     cfg.threads = 128;
     cfg.fast = which != 1;
+    const int rays = which == 2 ? traceRaysPerThread() : 1;
     int cap = std::min(dev.poolBound, cfg.fast ? 12 : 16);
     if(const char *e = getenv("PTB200_POOL_CAP"))
         cap = std::max(2, std::min(dev.poolBound, atoi(e)));
@@ -581,7 +614,7 @@ static int chooseConfig(PtbScene *s, int which, DeviceBuffer &overflow, CsgConfi
     if(cfg.fast)
     {
         cfg.stageProgram = (size_t)dev.fastWords * 16 <= 96 * 1024 ? 1 : 0;
-        cfg.smemBytes = fastSharedBytes(dev, cfg.cap, cfg.stageProgram);
+        cfg.smemBytes = fastSharedBytes(dev, cfg.cap, cfg.stageProgram, rays);
     }
     else
     {
@@ -600,7 +633,7 @@ static int chooseConfig(PtbScene *s, int which, DeviceBuffer &overflow, CsgConfi
     cfg.overflow = nullptr;
     if(dev.poolBound > cfg.cap)
     {
-        size_t bytes = (size_t)(dev.poolBound - cfg.cap) * 3 * sizeof(float) * cfg.ovfStride;
+        size_t bytes = (size_t)rays * (dev.poolBound - cfg.cap) * 3 * sizeof(float) * cfg.ovfStride;
         CU(overflow.ensure(bytes));
         cfg.overflow = (float *)overflow.p;
     }
@@ -623,7 +656,7 @@ extern "C" int ptb200_intersect_device(PtbScene *s, const void *d_origins4, cons
         return rc;
     if(n == 0)
         return PTB_OK;
-    launchIntersect(s->dev, cfg, (const float4 *)d_origins4, (const float4 *)d_dirs4, n, (PtbHit *)d_hits, (PtbSpan *)d_spans, max_spans, exact, (cudaStream_t)stream);
+    launchIntersect(s->dev, cfg, (const float4 *)d_origins4, (const float4 *)d_dirs4, n, (PtbHit *)d_hits, (PtbSpan *)d_spans, max_spans, exact, (flags & PTB_FLAG_ORIGIN0) != 0, (cudaStream_t)stream);
     CU(cudaGetLastError());
     return PTB_OK;
 }

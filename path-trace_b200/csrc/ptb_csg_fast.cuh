@@ -39,16 +39,25 @@ namespace ptb
 
 extern __shared__ uint4 ptbSmem[];
 
+// header.x: bits 0-3 one-hot kind (cheap bit tests, no jump table), 4-5 leaf action / control
+// sub-kind, 6 = shift the bit stack when the leaf misses (action == PUSH), 7 = the word has a tail
+// (operators to run, or an Intersection action), 8-11 nPost, 12-29 up to 9 operators (2 bits each),
+// 30 = union-only tail, 31 = leaf pair.  Sphere headers: z = -r^2, w = |t - c|^2 - r^2 (the constant
+// term for rays from the origin, i.e. all camera rays: include/path-trace.h:196)
 enum
 {
-    FK_END = 0,
     FK_SPHERE_XF = 1, // header {x, tags, -r^2, 0}, 3 rows of the folded matrix
     FK_PLANE = 2,     // header {x, tags, 0, 0}, float4 (n.xyz, D) in world space
-    FK_SPHERE = 3,    // header {x, tags, -r^2, 0}, float4 (-c.xyz, 0)
-    FK_OPS = 4,       // header only: operators that could not ride on the previous leaf
-    FK_SKIP = 5       // header only: x >> 4 = words to jump when the top list is empty warp-wide
+    FK_SPHERE = 4,    // header {x, tags, -r^2, 0}, float4 (-c.xyz, 0)
+    FK_CONTROL = 8,
+    FK_END = 8,              // control sub-kind 0
+    FK_OPS = 8 | (1 << 4),   // header only: operators that could not ride on the previous leaf
+    FK_SKIP = 8 | (2 << 4),  // header only: y = words to jump when the top list is empty warp-wide
+    FH_MISS_SHIFT = 1 << 6,
+    FH_TAIL = 1 << 7,
+    FH_UNION_TAIL = 1 << 30, // every operator of the tail is a Union (and the action is not Intersection)
+    FH_PAIR = 1u << 31       // SPHERE_XF without tail directly followed by another SPHERE_XF leaf
 };
-// header.x = kind | action << 4 | nPost << 8 | post << 12 (up to 10 operators, 2 bits each, first lowest)
 enum
 {
     FA_PUSH = 0, // no operator follows the leaf directly
@@ -57,7 +66,7 @@ enum
     FA_INTERSECTION = 3
 };
 #define PTB_FAST_THREADS 128
-#define PTB_FAST_MAX_POST 10
+#define PTB_FAST_MAX_POST 9
 #define PTB_FAST_MAX_STACK 32
 
 __device__ __forceinline__ uint4 lds128(uint32_t a)
@@ -123,9 +132,19 @@ struct FastPool
 
 struct FastCtx
 {
-    uint32_t prog; // shared address of the first program word (unused with a global program)
-    uint32_t stk;  // shared address of this thread's start stack
-    FastPool pool;
+    uint32_t prog;       // shared address of the first program word (unused with a global program)
+    uint32_t stk;        // shared address of this thread's start stack (ray 0)
+    uint32_t stkStride;  // bytes from ray r's start stack to ray r+1's
+    uint32_t poolStride; // bytes from ray r's pool to ray r+1's
+    size_t ovfRay;       // floats from ray r's overflow area to ray r+1's
+    FastPool pool;       // ray 0's pool
+    __device__ __forceinline__ FastPool poolOf(int r) const
+    {
+        FastPool p = pool;
+        p.base += (uint32_t)r * poolStride;
+        p.ovf += (size_t)r * ovfRay;
+        return p;
+    }
 };
 
 __device__ __forceinline__ float rcpApprox(float x)
@@ -156,6 +175,31 @@ static __device__ __noinline__ int fastMerge(uint32_t poolBase, int cap, float *
     FastPool pool;
     pool.base = poolBase, pool.cap = cap, pool.ovf = ovf, pool.ovfStride = ovfStride;
     const int kind = (int)op - FA_UNION + DK_UNION;
+    if(op == FA_UNION && b0 - a0 == 1 && top - b0 == 1)
+    { // the commonest real merge (two single spans), UnionSpanIterator::next unrolled: src/union.cpp:104-133
+        SpanRec A = pool.load(a0), B = pool.load(b0);
+        if(A.t1 < B.t0)
+            return top; // disjoint, already in order
+        if(B.t1 < A.t0)
+        {
+            pool.store(a0, B);
+            pool.store(b0, A);
+            return top;
+        }
+        if(A.t0 < B.t0)
+        {
+            if(A.t1 < B.t1)
+                copyEndFromEnd(A, B);
+            pool.store(a0, A);
+        }
+        else
+        {
+            if(A.t1 > B.t1)
+                copyEndFromEnd(B, A);
+            pool.store(a0, B);
+        }
+        return a0 + 1;
+    }
     if(b0 - a0 == 1 && top - b0 == 1)
         return mergeListsT(pool, kind, a0, b0, top, a0); // both inputs are in registers before the first output
     int end = mergeListsT(pool, kind, a0, b0, top, top);
@@ -233,117 +277,223 @@ static __device__ __noinline__ uint3 fastLeafHit(uint32_t poolBase, int cap, flo
     return make_uint3(bits, (uint32_t)ntop, sp);
 }
 
-// Runs the whole program for one ray, all 32 lanes of the warp together (SKIP words vote);
-// the root span list is pool slots [0, return).
-template <bool GP>
-__device__ __forceinline__ int evalFast(const FastCtx &c, const uint4 *__restrict__ gprog, V3 o, V3 d)
+
+
+// Discriminant of one folded transformed sphere: a = |d'|^2, b = oc.d', disc = b^2 - a c
+// (src/sphere.cpp:33-38 on the ray transformed by the folded matrix).  O0: the ray starts at the
+// world origin (every camera ray), so oc is the matrix translation and c is the header constant.
+template <bool O0>
+__device__ __forceinline__ void xfDisc(const uint4 &h, const uint4 &u0, const uint4 &u1, const uint4 &u2, V3 o, V3 d, float &a, float &b, float &disc)
+{
+    const float m00 = __uint_as_float(u0.x), m01 = __uint_as_float(u0.y), m02 = __uint_as_float(u0.z), m03 = __uint_as_float(u0.w);
+    const float m10 = __uint_as_float(u1.x), m11 = __uint_as_float(u1.y), m12 = __uint_as_float(u1.z), m13 = __uint_as_float(u1.w);
+    const float m20 = __uint_as_float(u2.x), m21 = __uint_as_float(u2.y), m22 = __uint_as_float(u2.z), m23 = __uint_as_float(u2.w);
+    float dx = fmaf(d.x, m00, fmaf(d.y, m01, d.z * m02));
+    float dy = fmaf(d.x, m10, fmaf(d.y, m11, d.z * m12));
+    float dz = fmaf(d.x, m20, fmaf(d.y, m21, d.z * m22));
+    a = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+    float cc;
+    if(O0)
+    {
+        b = fmaf(m03, dx, fmaf(m13, dy, m23 * dz));
+        cc = __uint_as_float(h.w);
+    }
+    else
+    {
+        float ox = fmaf(o.x, m00, fmaf(o.y, m01, fmaf(o.z, m02, m03)));
+        float oy = fmaf(o.x, m10, fmaf(o.y, m11, fmaf(o.z, m12, m13)));
+        float oz = fmaf(o.x, m20, fmaf(o.y, m21, fmaf(o.z, m22, m23)));
+        b = fmaf(ox, dx, fmaf(oy, dy, oz * dz));
+        cc = fmaf(ox, ox, fmaf(oy, oy, fmaf(oz, oz, __uint_as_float(h.z))));
+    }
+    disc = fmaf(b, b, -(a * cc));
+}
+
+// Leaf epilogue for one ray: the common case (miss) is one shift.
+__device__ __forceinline__ void fastLeafDone(const FastPool &pool, uint32_t hx, uint32_t tags, bool hit, float a, float b, float disc, FastState &st)
+{
+    if(hit)
+    { // src/sphere.cpp:44-46
+        float s = sqrtApprox(disc), ia = rcpApprox(a);
+        uint3 q = fastLeafHit(pool.base, pool.cap, pool.ovf, pool.ovfStride, (hx >> 4) & 3u, (-b - s) * ia, (-b + s) * ia, tags, st.bits, st.top, st.sp);
+        st.bits = q.x, st.top = (int)q.y, st.sp = q.z;
+    }
+    else
+        st.bits <<= (hx >> 6) & 1u;
+}
+
+// Runs the whole program for R rays per lane, all 32 lanes of the warp together (SKIP words
+// vote).  Ray r's root span list ends up in pool r, slots [0, topOut[r]).  (R = 2 was measured
+// slower than R = 1 on B200 — occupancy beats per-thread ILP here — and is kept for experiments.)
+template <bool GP, bool O0, int R>
+__device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restrict__ gprog, const V3 (&o)[R], const V3 (&d)[R], int (&topOut)[R])
 {
     const uint32_t W = 4u * PTB_FAST_THREADS;
-    FastState st;
-    st.bits = 0u, st.top = 0, st.sp = c.stk;
+    FastState st[R];
+#pragma unroll
+    for(int r = 0; r < R; r++)
+        st[r].bits = 0u, st[r].top = 0, st[r].sp = c.stk + (uint32_t)r * c.stkStride;
     uint32_t pc = GP ? 0u : c.prog; // GP: word index; else shared byte address
 #define PTB_PROG(i) (GP ? __ldg(gprog + pc + (i)) : lds128(pc + 16u * (i)))
 #define PTB_ADVANCE(n) (pc += GP ? (uint32_t)(n) : 16u * (uint32_t)(n))
     for(;;)
     {
-        const uint4 h = PTB_PROG(0);
-        const uint32_t kind = h.x & 15u;
-        if(kind <= FK_SPHERE)
+        uint4 h = PTB_PROG(0);
+        bool hit[R];
+        if(h.x & FK_SPHERE_XF)
         {
-            if(kind == FK_END)
-                break;
-            bool hit;
-            float t0, t1;
-            if(kind == FK_SPHERE_XF)
-            { // transform(m, ray) folded with `origin - centre`; src/sphere.cpp:33-43
+            if(h.x & FH_PAIR)
+            { // two tail-less... the first has no tail; both discriminants are computed together (ILP)
                 const uint4 u0 = PTB_PROG(1), u1 = PTB_PROG(2), u2 = PTB_PROG(3);
-                PTB_ADVANCE(4);
-                const float m00 = __uint_as_float(u0.x), m01 = __uint_as_float(u0.y), m02 = __uint_as_float(u0.z), m03 = __uint_as_float(u0.w);
-                const float m10 = __uint_as_float(u1.x), m11 = __uint_as_float(u1.y), m12 = __uint_as_float(u1.z), m13 = __uint_as_float(u1.w);
-                const float m20 = __uint_as_float(u2.x), m21 = __uint_as_float(u2.y), m22 = __uint_as_float(u2.z), m23 = __uint_as_float(u2.w);
-                float ox = fmaf(o.x, m00, fmaf(o.y, m01, fmaf(o.z, m02, m03)));
-                float oy = fmaf(o.x, m10, fmaf(o.y, m11, fmaf(o.z, m12, m13)));
-                float oz = fmaf(o.x, m20, fmaf(o.y, m21, fmaf(o.z, m22, m23)));
-                float dx = fmaf(d.x, m00, fmaf(d.y, m01, d.z * m02));
-                float dy = fmaf(d.x, m10, fmaf(d.y, m11, d.z * m12));
-                float dz = fmaf(d.x, m20, fmaf(d.y, m21, d.z * m22));
-                float a = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-                float b = fmaf(ox, dx, fmaf(oy, dy, oz * dz));
-                float cc = fmaf(ox, ox, fmaf(oy, oy, fmaf(oz, oz, __uint_as_float(h.z))));
-                float disc = fmaf(b, b, -(a * cc));
-                hit = disc > PTB_EPS;
-                if(hit)
+                const uint4 g = PTB_PROG(4), v0 = PTB_PROG(5), v1 = PTB_PROG(6), v2 = PTB_PROG(7);
+                PTB_ADVANCE(8);
+                float a0[R], b0[R], e0[R], a1[R], b1[R], e1[R];
+#pragma unroll
+                for(int r = 0; r < R; r++)
                 {
-                    float s = sqrtApprox(disc), ia = rcpApprox(a);
-                    t0 = (-b - s) * ia;
-                    t1 = (-b + s) * ia;
+                    xfDisc<O0>(h, u0, u1, u2, o[r], d[r], a0[r], b0[r], e0[r]);
+                    xfDisc<O0>(g, v0, v1, v2, o[r], d[r], a1[r], b1[r], e1[r]);
                 }
-            }
-            else if(kind == FK_PLANE)
-            { // PlaneSpanIterator::init, src/plane.cpp:35-63, on the world-space plane
-                const uint4 u0 = PTB_PROG(1);
-                PTB_ADVANCE(2);
-                float nx = __uint_as_float(u0.x), ny = __uint_as_float(u0.y), nz = __uint_as_float(u0.z);
-                float divisor = fmaf(d.x, nx, fmaf(d.y, ny, d.z * nz));
-                float numerator = -fmaf(o.x, nx, fmaf(o.y, ny, fmaf(o.z, nz, __uint_as_float(u0.w))));
-                float t = numerator * rcpApprox(divisor);
-                bool parallel = fabsf(divisor) < PTB_EPS * PTB_EPS || !(fabsf(t) < PTB_MAX_VALUE);
-                hit = !parallel || fabsf(numerator) < PTB_EPS * PTB_EPS;
-                bool lo = !parallel && divisor < 0.0f, hi = !parallel && !(divisor < 0.0f);
-                t0 = lo ? t : -PTB_MAX_VALUE;
-                t1 = hi ? t : PTB_MAX_VALUE;
+#pragma unroll
+                for(int r = 0; r < R; r++)
+                {
+                    fastLeafDone(c.poolOf(r), h.x, h.y, e0[r] > PTB_EPS, a0[r], b0[r], e0[r], st[r]);
+                    hit[r] = e1[r] > PTB_EPS;
+                    fastLeafDone(c.poolOf(r), g.x, g.y, hit[r], a1[r], b1[r], e1[r], st[r]);
+                }
+                h = g; // the second leaf's tail, if any, runs below
             }
             else
             {
-                const uint4 u0 = PTB_PROG(1);
-                PTB_ADVANCE(2);
-                float ox = o.x + __uint_as_float(u0.x), oy = o.y + __uint_as_float(u0.y), oz = o.z + __uint_as_float(u0.z);
-                float a = fmaf(d.x, d.x, fmaf(d.y, d.y, d.z * d.z));
-                float b = fmaf(ox, d.x, fmaf(oy, d.y, oz * d.z));
-                float cc = fmaf(ox, ox, fmaf(oy, oy, fmaf(oz, oz, __uint_as_float(h.z))));
-                float disc = fmaf(b, b, -(a * cc));
-                hit = disc > PTB_EPS;
-                if(hit)
+                const uint4 u0 = PTB_PROG(1), u1 = PTB_PROG(2), u2 = PTB_PROG(3);
+                PTB_ADVANCE(4);
+#pragma unroll
+                for(int r = 0; r < R; r++)
                 {
-                    float s = sqrtApprox(disc), ia = rcpApprox(a);
-                    t0 = (-b - s) * ia;
-                    t1 = (-b + s) * ia;
+                    float a, b, e;
+                    xfDisc<O0>(h, u0, u1, u2, o[r], d[r], a, b, e);
+                    hit[r] = e > PTB_EPS;
+                    fastLeafDone(c.poolOf(r), h.x, h.y, hit[r], a, b, e, st[r]);
                 }
             }
-            const uint32_t action = (h.x >> 4) & 3u;
-            if(hit)
+        }
+        else if(h.x & FK_PLANE)
+        { // PlaneSpanIterator::init, src/plane.cpp:35-63, on the world-space plane
+            const uint4 u0 = PTB_PROG(1);
+            PTB_ADVANCE(2);
+            const float nx = __uint_as_float(u0.x), ny = __uint_as_float(u0.y), nz = __uint_as_float(u0.z);
+#pragma unroll
+            for(int r = 0; r < R; r++)
             {
-                uint3 r = fastLeafHit(c.pool.base, c.pool.cap, c.pool.ovf, c.pool.ovfStride, action, t0, t1, h.y, st.bits, st.top, st.sp);
-                st.bits = r.x, st.top = (int)r.y, st.sp = r.z;
-            }
-            else if(action == FA_PUSH)
-                st.bits <<= 1;
-            else if(action == FA_INTERSECTION && (st.bits & 1u))
-            { // A n {} = {}: A's spans are dropped
-                st.sp -= W;
-                st.top = (int)lds32(st.sp);
-                st.bits &= ~1u;
+                float divisor = fmaf(d[r].x, nx, fmaf(d[r].y, ny, d[r].z * nz));
+                float numerator = O0 ? -__uint_as_float(u0.w) : -fmaf(o[r].x, nx, fmaf(o[r].y, ny, fmaf(o[r].z, nz, __uint_as_float(u0.w))));
+                float t = numerator * rcpApprox(divisor);
+                bool parallel = fabsf(divisor) < PTB_EPS * PTB_EPS || !(fabsf(t) < PTB_MAX_VALUE);
+                hit[r] = !parallel || fabsf(numerator) < PTB_EPS * PTB_EPS;
+                bool lo = !parallel && divisor < 0.0f, hi = !parallel && !(divisor < 0.0f);
+                if(hit[r])
+                {
+                    FastPool pool = c.poolOf(r);
+                    uint3 q = fastLeafHit(pool.base, pool.cap, pool.ovf, pool.ovfStride, (h.x >> 4) & 3u, lo ? t : -PTB_MAX_VALUE, hi ? t : PTB_MAX_VALUE, h.y, st[r].bits,
+                                          st[r].top, st[r].sp);
+                    st[r].bits = q.x, st[r].top = (int)q.y, st[r].sp = q.z;
+                }
+                else
+                    st[r].bits <<= (h.x >> 6) & 1u;
             }
         }
-        else if(kind == FK_SKIP)
+        else if(h.x & FK_SPHERE)
         {
-            PTB_ADVANCE(1);
-            if(!__any_sync(0xFFFFFFFFu, st.bits & 1u))
-                PTB_ADVANCE(h.x >> 4);
-            continue;
+            const uint4 u0 = PTB_PROG(1);
+            PTB_ADVANCE(2);
+#pragma unroll
+            for(int r = 0; r < R; r++)
+            {
+                float a = fmaf(d[r].x, d[r].x, fmaf(d[r].y, d[r].y, d[r].z * d[r].z));
+                float b, cc;
+                if(O0)
+                {
+                    b = fmaf(__uint_as_float(u0.x), d[r].x, fmaf(__uint_as_float(u0.y), d[r].y, __uint_as_float(u0.z) * d[r].z));
+                    cc = __uint_as_float(h.w);
+                }
+                else
+                {
+                    float ox = o[r].x + __uint_as_float(u0.x), oy = o[r].y + __uint_as_float(u0.y), oz = o[r].z + __uint_as_float(u0.z);
+                    b = fmaf(ox, d[r].x, fmaf(oy, d[r].y, oz * d[r].z));
+                    cc = fmaf(ox, ox, fmaf(oy, oy, fmaf(oz, oz, __uint_as_float(h.z))));
+                }
+                float e = fmaf(b, b, -(a * cc));
+                hit[r] = e > PTB_EPS;
+                fastLeafDone(c.poolOf(r), h.x, h.y, hit[r], a, b, e, st[r]);
+            }
         }
         else
+        { // control word
+            const uint32_t sub = (h.x >> 4) & 3u;
+            if(sub == 0u)
+                break;
             PTB_ADVANCE(1);
-        uint32_t npost = (h.x >> 8) & 15u, post = h.x >> 12;
+            if(sub == 2u)
+            {
+                uint32_t live = 0u;
+#pragma unroll
+                for(int r = 0; r < R; r++)
+                    live |= st[r].bits;
+                if(!__any_sync(0xFFFFFFFFu, live & 1u))
+                    PTB_ADVANCE(h.y);
+                continue;
+            }
+#pragma unroll
+            for(int r = 0; r < R; r++)
+                hit[r] = true; // an OPS word has no leaf: nothing to drop below
+        }
+        if(!(h.x & FH_TAIL))
+            continue;
+        uint32_t npost = (h.x >> 8) & 15u;
+        if(h.x & FH_UNION_TAIL)
+        { // a run of Unions: bit arithmetic unless both lists have spans
+            do
+            {
+#pragma unroll
+                for(int r = 0; r < R; r++)
+                {
+                    if((st[r].bits & 3u) == 3u)
+                    {
+                        FastPool pool = c.poolOf(r);
+                        uint3 q = fastOpSlow(pool.base, pool.cap, pool.ovf, pool.ovfStride, FA_UNION, 3u, st[r].top, st[r].sp);
+                        st[r].top = (int)q.y, st[r].sp = q.z;
+                    }
+                    st[r].bits = (st[r].bits >> 1) | (st[r].bits & 1u);
+                }
+            } while(--npost);
+            continue;
+        }
+        if(((h.x >> 4) & 3u) == FA_INTERSECTION && !(h.x & FK_CONTROL))
+        { // A n {} = {}: a missed leaf drops the spans of the list below
+#pragma unroll
+            for(int r = 0; r < R; r++)
+                if(!hit[r] && (st[r].bits & 1u))
+                {
+                    st[r].sp -= W;
+                    st[r].top = (int)lds32(st[r].sp);
+                    st[r].bits &= ~1u;
+                }
+        }
+        uint32_t post = h.x >> 12;
         while(npost)
         {
-            fastOp(c.pool, (post & 3u) + FA_UNION, st);
+            const uint32_t op = (post & 3u) + FA_UNION;
+#pragma unroll
+            for(int r = 0; r < R; r++)
+                fastOp(c.poolOf(r), op, st[r]);
             post >>= 2, npost--;
         }
     }
 #undef PTB_PROG
 #undef PTB_ADVANCE
-    return st.top;
+#pragma unroll
+    for(int r = 0; r < R; r++)
+        topOut[r] = st[r].top;
 }
 
 } // namespace ptb

@@ -18,6 +18,9 @@ namespace ptb
 {
 
 #define PTB_SHADE_THREADS 128
+#ifndef PTB_TRACE_RAYS
+#define PTB_TRACE_RAYS 1
+#endif
 #ifndef PTB_TRACE_MIN_CTAS
 #define PTB_TRACE_MIN_CTAS 8
 #endif
@@ -30,13 +33,14 @@ size_t csgSharedBytes(const DevScene &sc, int threads, int cap, bool stageProgra
     bytes += (size_t)sc.maxStack * threads * 2;          // stack-entry start offsets (u16)
     return (bytes + 15) & ~(size_t)15;
 }
-size_t fastSharedBytes(const DevScene &sc, int cap, bool stageProgram)
+size_t fastSharedBytes(const DevScene &sc, int cap, bool stageProgram, int rays)
 {
     size_t bytes = stageProgram ? (size_t)sc.fastWords * 16 : 0;
-    bytes += (size_t)cap * PTB_FAST_THREADS * 12;               // t0, t1, tags
-    bytes += (size_t)(sc.maxStack + 1) * PTB_FAST_THREADS * 4;  // list-start stack (u32)
+    bytes += (size_t)rays * cap * PTB_FAST_THREADS * 12;               // t0, t1, tags
+    bytes += (size_t)rays * (sc.maxStack + 1) * PTB_FAST_THREADS * 4;  // list-start stack (u32)
     return (bytes + 15) & ~(size_t)15;
 }
+int traceRaysPerThread() { return PTB_TRACE_RAYS; }
 
 struct CsgShared
 {
@@ -72,8 +76,9 @@ __device__ __forceinline__ CsgShared setupCsg(const DevScene &sc, int cap, int s
     return s;
 }
 
-// Fast evaluator: stage the program (unless GP: it stays in global memory) and lay out pool + stack.
-template <bool GP>
+// Fast evaluator: stage the program (unless GP: it stays in global memory) and lay out the pools
+// and start stacks of the R rays each thread carries.
+template <bool GP, int R>
 __device__ __forceinline__ FastCtx setupFast(const DevScene &sc, int cap, float *overflow, size_t ovfStride)
 {
     FastCtx c;
@@ -86,11 +91,14 @@ __device__ __forceinline__ FastCtx setupFast(const DevScene &sc, int cap, float 
             sts128(base + 16u * i, __ldg(sc.fastProgram + i));
     }
     c.prog = base;
+    c.poolStride = (uint32_t)cap * (12u * PTB_FAST_THREADS);
+    c.stkStride = (uint32_t)(sc.maxStack + 1) * (4u * PTB_FAST_THREADS);
     c.pool.base = base + 16u * words + 4u * threadIdx.x;
     c.pool.cap = cap;
     c.pool.ovf = overflow ? overflow + (size_t)blockIdx.x * PTB_FAST_THREADS + threadIdx.x : nullptr;
     c.pool.ovfStride = ovfStride;
-    c.stk = c.pool.base + (uint32_t)cap * (12u * PTB_FAST_THREADS);
+    c.ovfRay = (size_t)(sc.poolBound > cap ? sc.poolBound - cap : 0) * 3 * ovfStride;
+    c.stk = c.pool.base + (uint32_t)R * c.poolStride;
     __syncthreads();
     return c;
 }
@@ -179,12 +187,12 @@ __global__ void __launch_bounds__(128) intersectExactKernel(DevScene sc, int cap
 }
 
 // Fast policy: the evaluator the renderer runs.
-template <bool GP>
+template <bool GP, bool O0>
 __global__ void __launch_bounds__(PTB_FAST_THREADS) intersectFastKernel(DevScene sc, int cap, float *overflow, size_t ovfStride, const float4 *__restrict__ origins,
                                                                         const float4 *__restrict__ dirs, size_t n, PtbHit *__restrict__ hits, PtbSpan *__restrict__ spans,
                                                                         int maxSpans)
 {
-    FastCtx cx = setupFast<GP>(sc, cap, overflow, ovfStride);
+    FastCtx cx = setupFast<GP, 1>(sc, cap, overflow, ovfStride);
     size_t stride = (size_t)gridDim.x * PTB_FAST_THREADS;
     // warp-uniform trip count: the evaluator needs all 32 lanes (idle lanes carry a null ray)
     for(size_t base = (size_t)blockIdx.x * PTB_FAST_THREADS + (threadIdx.x & ~31u); base < n; base += stride)
@@ -197,7 +205,10 @@ __global__ void __launch_bounds__(PTB_FAST_THREADS) intersectFastKernel(DevScene
             float4 o4 = __ldg(&origins[i]), d4 = __ldg(&dirs[i]);
             o = mk(o4.x, o4.y, o4.z), d = mk(d4.x, d4.y, d4.z);
         }
-        int nSpans = evalFast<GP>(cx, sc.fastProgram, o, d);
+        V3 oo[1] = {o}, dd[1] = {d};
+        int tops[1];
+        evalFast<GP, O0, 1>(cx, sc.fastProgram, oo, dd, tops);
+        int nSpans = tops[0];
         if(valid)
         {
             Hit hit;
@@ -209,22 +220,35 @@ __global__ void __launch_bounds__(PTB_FAST_THREADS) intersectFastKernel(DevScene
 }
 
 void launchIntersect(const DevScene &sc, const CsgConfig &cfg, const float4 *origins, const float4 *dirs, size_t n, PtbHit *hits, PtbSpan *spans, int maxSpans,
-                     bool exact, cudaStream_t stream)
+                     bool exact, bool origin0, cudaStream_t stream)
 {
     if(exact)
     {
         cudaFuncSetAttribute(intersectExactKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
         intersectExactKernel<<<cfg.blocks, cfg.threads, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.stageProgram, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans, maxSpans);
     }
-    else if(cfg.stageProgram)
-    {
-        cudaFuncSetAttribute(intersectFastKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
-        intersectFastKernel<false><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans, maxSpans);
-    }
     else
     {
-        cudaFuncSetAttribute(intersectFastKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
-        intersectFastKernel<true><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans, maxSpans);
+#define PTB_LAUNCH_INTERSECT(GP, O0)                                                                                                                                      \
+    cudaFuncSetAttribute(intersectFastKernel<GP, O0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);                                                   \
+    intersectFastKernel<GP, O0><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans, maxSpans)
+        if(cfg.stageProgram && origin0)
+        {
+            PTB_LAUNCH_INTERSECT(false, true);
+        }
+        else if(cfg.stageProgram)
+        {
+            PTB_LAUNCH_INTERSECT(false, false);
+        }
+        else if(origin0)
+        {
+            PTB_LAUNCH_INTERSECT(true, true);
+        }
+        else
+        {
+            PTB_LAUNCH_INTERSECT(true, false);
+        }
+#undef PTB_LAUNCH_INTERSECT
     }
 }
 
@@ -277,41 +301,57 @@ __device__ __forceinline__ void cameraSample(const RenderPass &pass, unsigned nP
     ps.depth = (unsigned)pass.maxDepth;
 }
 
-// Evaluates the CSG program for one ray per lane (all 32 lanes take part: SKIP words vote) and
-// packs the first boundary with t >= eps.
-template <bool GP>
-__device__ __forceinline__ uint2 traceOne(const DevScene &sc, const FastCtx &cx, V3 o, V3 d)
+// Evaluates the CSG program for PTB_TRACE_RAYS rays per lane (all 32 lanes take part: SKIP words
+// vote) and packs each ray's first boundary with t >= eps.
+template <bool GP, bool O0>
+__device__ __forceinline__ void traceRays(const DevScene &sc, const FastCtx &cx, const V3 (&o)[PTB_TRACE_RAYS], const V3 (&d)[PTB_TRACE_RAYS], uint2 (&h)[PTB_TRACE_RAYS])
 {
-    int nSpans = evalFast<GP>(cx, sc.fastProgram, o, d);
-    float t = -1.f;
-    uint32_t tag = 0u;
-    int kind = firstHit(cx.pool, nSpans, t, tag);
-    return make_uint2(__float_as_uint(t), ((uint32_t)kind << 16) | tag);
+    int tops[PTB_TRACE_RAYS];
+    evalFast<GP, O0, PTB_TRACE_RAYS>(cx, sc.fastProgram, o, d, tops);
+#pragma unroll
+    for(int r = 0; r < PTB_TRACE_RAYS; r++)
+    {
+        float t = -1.f;
+        uint32_t tag = 0u;
+        int kind = firstHit(cx.poolOf(r), tops[r], t, tag);
+        h[r] = make_uint2(__float_as_uint(t), ((uint32_t)kind << 16) | tag);
+    }
 }
 
+// A warp takes 32 * PTB_TRACE_RAYS consecutive rays per trip: lane l carries rays l, l + 32, ...
 template <bool GP>
 __global__ void __launch_bounds__(PTB_FAST_THREADS, PTB_TRACE_MIN_CTAS) tracePrimaryKernel(DevScene sc, int cap, float *overflow, size_t ovfStride, RenderPass pass,
                                                                                            uint2 *__restrict__ hits)
 {
-    FastCtx cx = setupFast<GP>(sc, cap, overflow, ovfStride);
+    FastCtx cx = setupFast<GP, PTB_TRACE_RAYS>(sc, cap, overflow, ovfStride);
     const unsigned nPix = (unsigned)pass.rw * (unsigned)pass.rh;
     const unsigned long long total = (unsigned long long)nPix * (unsigned)pass.samplesThisPass;
-    const unsigned long long stride = (unsigned long long)gridDim.x * PTB_FAST_THREADS;
+    const unsigned long long stride = (unsigned long long)gridDim.x * PTB_FAST_THREADS * PTB_TRACE_RAYS;
     // warp-uniform trip count; idle lanes of the last warp carry a null ray
-    for(unsigned long long base = (unsigned long long)blockIdx.x * PTB_FAST_THREADS + (threadIdx.x & ~31u); base < total; base += stride)
+    for(unsigned long long base = ((unsigned long long)blockIdx.x * PTB_FAST_THREADS + (threadIdx.x & ~31u)) * PTB_TRACE_RAYS; base < total; base += stride)
     {
-        unsigned long long i = base + (threadIdx.x & 31u);
-        bool valid = i < total;
-        V3 o = mk(0.f, 0.f, 0.f), d = o;
-        if(valid)
+        V3 o[PTB_TRACE_RAYS], d[PTB_TRACE_RAYS];
+#pragma unroll
+        for(int r = 0; r < PTB_TRACE_RAYS; r++)
         {
-            PathState ps;
-            cameraSample(pass, nPix, i, ps);
-            d = ps.d;
+            unsigned long long i = base + 32u * r + (threadIdx.x & 31u);
+            o[r] = d[r] = mk(0.f, 0.f, 0.f);
+            if(i < total)
+            {
+                PathState ps;
+                cameraSample(pass, nPix, i, ps);
+                d[r] = ps.d;
+            }
         }
-        uint2 h = traceOne<GP>(sc, cx, o, d);
-        if(valid)
-            __stcs(&hits[i], h);
+        uint2 h[PTB_TRACE_RAYS];
+        traceRays<GP, true>(sc, cx, o, d, h);
+#pragma unroll
+        for(int r = 0; r < PTB_TRACE_RAYS; r++)
+        {
+            unsigned long long i = base + 32u * r + (threadIdx.x & 31u);
+            if(i < total)
+                __stcs(&hits[i], h[r]);
+        }
     }
 }
 
@@ -322,21 +362,31 @@ __global__ void __launch_bounds__(PTB_FAST_THREADS, PTB_TRACE_MIN_CTAS) traceQue
     const unsigned total = *inCount;
     if(total == 0u)
         return;
-    FastCtx cx = setupFast<GP>(sc, cap, overflow, ovfStride);
-    const unsigned long long stride = (unsigned long long)gridDim.x * PTB_FAST_THREADS;
-    for(unsigned long long base = (unsigned long long)blockIdx.x * PTB_FAST_THREADS + (threadIdx.x & ~31u); base < total; base += stride)
+    FastCtx cx = setupFast<GP, PTB_TRACE_RAYS>(sc, cap, overflow, ovfStride);
+    const unsigned long long stride = (unsigned long long)gridDim.x * PTB_FAST_THREADS * PTB_TRACE_RAYS;
+    for(unsigned long long base = ((unsigned long long)blockIdx.x * PTB_FAST_THREADS + (threadIdx.x & ~31u)) * PTB_TRACE_RAYS; base < total; base += stride)
     {
-        unsigned long long i = base + (threadIdx.x & 31u);
-        bool valid = i < total;
-        V3 o = mk(0.f, 0.f, 0.f), d = o;
-        if(valid)
+        V3 o[PTB_TRACE_RAYS], d[PTB_TRACE_RAYS];
+#pragma unroll
+        for(int r = 0; r < PTB_TRACE_RAYS; r++)
         {
-            float4 a = __ldg(&in.q0[i]), b = __ldg(&in.q1[i]);
-            o = mk(a.x, a.y, a.z), d = mk(b.x, b.y, b.z);
+            unsigned long long i = base + 32u * r + (threadIdx.x & 31u);
+            o[r] = d[r] = mk(0.f, 0.f, 0.f);
+            if(i < total)
+            {
+                float4 a = __ldg(&in.q0[i]), b = __ldg(&in.q1[i]);
+                o[r] = mk(a.x, a.y, a.z), d[r] = mk(b.x, b.y, b.z);
+            }
         }
-        uint2 h = traceOne<GP>(sc, cx, o, d);
-        if(valid)
-            __stcs(&hits[i], h);
+        uint2 h[PTB_TRACE_RAYS];
+        traceRays<GP, false>(sc, cx, o, d, h);
+#pragma unroll
+        for(int r = 0; r < PTB_TRACE_RAYS; r++)
+        {
+            unsigned long long i = base + 32u * r + (threadIdx.x & 31u);
+            if(i < total)
+                __stcs(&hits[i], h[r]);
+        }
     }
 }
 
@@ -568,7 +618,7 @@ int csgBlocksPerSm(int which, int threads, size_t smemBytes, bool globalProgram)
     if(which == 1)
         return occupancyOf(intersectExactKernel, threads, smemBytes);
     if(which == 0)
-        return globalProgram ? occupancyOf(intersectFastKernel<true>, threads, smemBytes) : occupancyOf(intersectFastKernel<false>, threads, smemBytes);
+        return globalProgram ? occupancyOf(intersectFastKernel<true, false>, threads, smemBytes) : occupancyOf(intersectFastKernel<false, false>, threads, smemBytes);
     return globalProgram ? occupancyOf(tracePrimaryKernel<true>, threads, smemBytes) : occupancyOf(tracePrimaryKernel<false>, threads, smemBytes);
 }
 } // namespace ptb

@@ -42,7 +42,7 @@ struct RenderPass
 };
 
 void launchIntersect(const DevScene &sc, const CsgConfig &cfg, const float4 *origins, const float4 *dirs, size_t n, PtbHit *hits, PtbSpan *spans, int maxSpans,
-                     bool exact, cudaStream_t stream);
+                     bool exact, bool origin0, cudaStream_t stream);
 // Trace stage of the first wavefront level: camera rays for rw*rh*samplesThisPass samples -> hits[i].
 void launchTracePrimary(const DevScene &sc, const CsgConfig &cfg, const RenderPass &pass, uint2 *hits, cudaStream_t stream);
 // Trace stage of a bounce level: *inCount rays of `in` -> hits[i].
@@ -58,7 +58,8 @@ void launchScatterSample(const float *normal, const float *refl, float scatter, 
 // FMA-chain microbenchmark: returns lane-FMAs executed.
 double launchFmaPeak(int blocks, int threads, int iters, cudaStream_t stream);
 size_t csgSharedBytes(const DevScene &sc, int threads, int cap, bool stageProgram);
-size_t fastSharedBytes(const DevScene &sc, int cap, bool stageProgram);
+size_t fastSharedBytes(const DevScene &sc, int cap, bool stageProgram, int rays);
+int traceRaysPerThread(); // rays each thread of the trace kernels carries
 
 } // namespace ptb
 

@@ -16,6 +16,7 @@ PRODUCT_LIB = os.path.join(PKG_ROOT, "libptb200.so")
 PTB_FLAG_EXACT = 1
 PTB_FLAG_BILINEAR = 2
 PTB_FLAG_REJECTION = 4
+PTB_FLAG_ORIGIN0 = 8
 PTB_HIT_MISS, PTB_HIT_ENTER, PTB_HIT_EXIT = 0, 1, 2
 
 

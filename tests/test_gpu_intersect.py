@@ -28,8 +28,8 @@ def assert_exact(sc, flat, o, d, max_spans):
     return oh, osp
 
 
-def assert_fast(sc, flat, o, d, oh, max_flagged=0.02):
-    gh, _ = sc.intersect(o, d, 0, 0)
+def assert_fast(sc, flat, o, d, oh, max_flagged=0.02, flags=0):
+    gh, _ = sc.intersect(o, d, 0, flags)
     topo, illcond = flag_grazing(flat.desc, o, d)
     ok = ~topo
     assert (~ok).mean() <= max_flagged, "too many rays flagged grazing: %.4f" % (~ok).mean()
@@ -85,6 +85,9 @@ def test_camera_rays_on_image_configs(name):
     d[n // 2:] = rs.normal(size=(n - n // 2, 3))
     oh, _ = assert_exact(sc, flat, o, d, 10)
     assert_fast(sc, flat, o, d, oh, max_flagged=0.05)
+    # the camera-ray variant of the evaluator (origin folded into per-primitive constants)
+    h = n // 2
+    assert_fast(sc, flat, o[:h], d[:h], oh[:h], max_flagged=0.05, flags=capi.PTB_FLAG_ORIGIN0)
 
 
 def test_pool_overflow_path_matches(monkeypatch):
