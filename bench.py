@@ -96,7 +96,7 @@ def cpu_reference_rate(name, seconds, width, height):
     all host cores: the 192x108-style lattice of the workload's image plane, rows until `seconds`."""
     import common
     cores = os.cpu_count() or 1
-    step = 20
+    step = int(os.environ.get("PTB200_REF_LATTICE", "4"))  # rows of the lattice are rendered until `seconds` is up
     nx, ny = width // step, height // step
     flags = open("/proc/cpuinfo").read() if os.path.exists("/proc/cpuinfo") else ""
     kind, info = "port", None
@@ -179,14 +179,15 @@ def run_ours(args):
     host_image = torch.empty((height, width, 4), pin_memory=True)
     params = device.default_params(width, height, spp // world_size, seed=0xB200, sample_offset=rank, sample_stride=world_size, samples_per_pass=args.samples_per_pass)
 
+    from ptb200 import multi
+
+    def make_params(**kw):
+        return device.default_params(width, height, seed=0xB200, samples_per_pass=args.samples_per_pass, **kw)
+
     def step(want_stats):
         accum.zero_()  # 132 MB write (> L2): also evicts the previous step's lines
-        st = scene.render_accumulate(params, accum, stream, want_stats)
-        if world_size > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
-        if rank == 0:
-            device.resolve(accum, rgba, stream)
-        return st
+        return multi.render_sharded(lambda p, a: scene.render_accumulate(p, a, stream, want_stats), lambda a, o: device.resolve(a, o, stream),
+                                    make_params, spp, accum, rgba, dist if world_size > 1 else None)
 
     def barrier():
         if world_size > 1:
@@ -256,8 +257,16 @@ def run_ours(args):
     fma_per_s, implied_mhz = device.fp32_peak()
     fpr = flops_per_ray(flat.desc)
     stage_ms = st.ms_primary + st.ms_bounce
-    stage_rays = st.rays
-    achieved = stage_rays * fpr / (stage_ms * 1e-3) / 1e12 if stage_ms > 0 else 0.0
+    # roofline kernel = the primary TRACE kernel (tracePrimaryKernel): its launches are timed alone with
+    # CUDA events on the render stream inside the library (PtbStats.ms_trace_primary)
+    n_trace_launches = max(1, int(st.launches) // (2 + 2 * 16))
+    trace_ms = st.ms_trace_primary
+    achieved = st.rays_primary * fpr / (trace_ms * 1e-3) / 1e12 if trace_ms > 0 else 0.0
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
+    except Exception:
+        pass
     peak = 2 * fma_per_s / 1e12
     peaks = {}
     try:
@@ -278,12 +287,13 @@ def run_ours(args):
                 "d2h_bytes_per_step": width * height * 16, "what": "ptb200_scene_create (uploads scene + images) + ptb200_render into a host buffer + destroy, per step"},
         "gpu_launches": int(launches / world_size) * args.steps + args.steps * (1 if rank == 0 else 0),
         "clocks": sampler.summary(),
-        "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": None,
-                     "kernel": "primaryKernel + bounceKernel (rank 0)", "flops_per_ray_model": fpr, "stage_ms": stage_ms,
+        "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic,
+                     "kernel": "tracePrimaryKernel (rank 0): %d launches, %.3f ms average, %.0f Mrays/s" % (n_trace_launches, trace_ms / n_trace_launches, st.rays_primary / (trace_ms * 1e-3) / 1e6 if trace_ms > 0 else 0.0),
+                     "flops_per_ray_model": fpr, "whole_wavefront": {"achieved": st.rays * fpr / (stage_ms * 1e-3) / 1e12 if stage_ms > 0 else 0.0, "stage_ms": stage_ms},
                      "peak_source": "ptb200_fp32_peak FMA-chain microbenchmark on this GPU (MEASURED_PEAKS.json has no FP32 entry); %.2f T lane-FMA/s = 128 lanes x %d SMs x %.0f MHz" % (fma_per_s / 1e12, torch.cuda.get_device_properties(0).multi_processor_count, implied_mhz),
                      "hbm_queues": {"bound": "hbm", "achieved": queue_bytes / world_size / (stage_ms * 1e-3) / 1e9 if stage_ms > 0 else 0.0, "peak": hbm_peak, "unit": "GB/s",
-                                    "frac": queue_bytes / world_size / (stage_ms * 1e-3) / 1e9 / hbm_peak if stage_ms > 0 else None, "bytes_per_queued_ray": 128}},
-        "stage_ms": {"primary": st.ms_primary, "bounce": st.ms_bounce, "total": st.ms_total},
+                                    "frac": queue_bytes / world_size / (stage_ms * 1e-3) / 1e9 / hbm_peak if stage_ms > 0 else None, "bytes_per_ray": "16 B hit record + 176 B per queued ray (64 written, 64 + 32 read, 16 hit)"}},
+        "stage_ms": {"primary": st.ms_primary, "bounce": st.ms_bounce, "total": st.ms_total, "trace_primary": st.ms_trace_primary, "trace_bounce": st.ms_trace_bounce},
         "cpu_baseline": cpu,
     }
     print(json.dumps(out))

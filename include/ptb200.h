@@ -189,11 +189,13 @@ typedef struct PtbStats {
     uint64_t launches;       /* kernels launched by this call                                      */
     uint64_t queue_bytes;    /* bytes read + written through the HBM ray queues                    */
     float ms_total;          /* device time of the whole call (CUDA events on the render stream)   */
-    float ms_primary;        /* ... of the primary (raygen+intersect+shade) kernels                */
-    float ms_bounce;         /* ... of the bounce (queue -> intersect+shade -> queue) kernels      */
+    float ms_primary;        /* ... of the primary level (camera rays: trace + shade kernels)      */
+    float ms_bounce;         /* ... of the bounce levels (queue -> trace -> shade -> queue)        */
     float ms_resolve;        /* ... of the framebuffer resolve kernel                              */
     uint64_t rays_primary;   /* rays traced by the primary kernels                                 */
     uint64_t rays_bounce;    /* rays traced by the bounce kernels                                  */
+    float ms_trace_primary;  /* ... of the primary TRACE kernel alone (the roofline kernel)        */
+    float ms_trace_bounce;   /* ... of the bounce TRACE kernels alone                              */
 } PtbStats;
 
 /* ---- entry points --------------------------------------------------------------------------- */

@@ -830,7 +830,8 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
         q[k].q0 = base, q[k].q1 = base + capacity, q[k].q2 = base + 2 * capacity, q[k].q3 = base + 3 * capacity;
     }
     const bool timed = stats != nullptr;
-    size_t nEvents = timed ? (size_t)nPasses * 3 : 0;
+    const int evPerPass = 3 + 2 * p->max_depth; // start, trace0, shade0, then trace/shade of every bounce level
+    size_t nEvents = timed ? (size_t)nPasses * evPerPass : 0;
     while(sx.events.size() < nEvents)
     {
         cudaEvent_t e;
@@ -851,19 +852,24 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
         unsigned *c = (unsigned *)sx.counters.p + (size_t)i * (stages + 1);
         pass.samplesThisPass = std::min(perPass, p->spp - i * perPass);
         pass.sampleBase = p->sample_offset + i * perPass * p->sample_stride;
+        cudaEvent_t *ev = timed ? &sx.events[(size_t)i * evPerPass] : nullptr;
         if(timed)
-            CU(cudaEventRecord(sx.events[3 * i], stream));
+            CU(cudaEventRecord(ev[0], stream));
         launchTracePrimary(s->dev, cfg, pass, hits, stream);
+        if(timed)
+            CU(cudaEventRecord(ev[1], stream));
         launchShade(s->dev, shadeBlocks, true, pass, accum, hits, q[0], nullptr, q[0], c, stream);
         if(timed)
-            CU(cudaEventRecord(sx.events[3 * i + 1], stream));
+            CU(cudaEventRecord(ev[2], stream));
         for(int b = 1; b <= p->max_depth; b++)
         {
             launchTraceQueue(s->dev, cfg, q[(b - 1) & 1], c + (b - 1), hits, stream);
+            if(timed)
+                CU(cudaEventRecord(ev[1 + 2 * b], stream));
             launchShade(s->dev, shadeBlocks, false, pass, accum, hits, q[(b - 1) & 1], c + (b - 1), q[b & 1], c + b, stream);
+            if(timed)
+                CU(cudaEventRecord(ev[2 + 2 * b], stream));
         }
-        if(timed)
-            CU(cudaEventRecord(sx.events[3 * i + 2], stream));
         launches += 2 + 2 * (uint64_t)p->max_depth;
         CU(cudaGetLastError());
     }
@@ -888,21 +894,31 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
         uint64_t primary = nPix * (uint64_t)std::min(perPass, p->spp - i * perPass);
         stats->paths += primary;
         stats->rays_primary += primary;
-        stats->queue_bytes += 64ull * c[0];
+        // algorithmic HBM traffic of the wavefront: 8 B hit record written + read per ray, 64 B per
+        // queued ray written by shade and read back by shade, of which trace re-reads 32 B (o, d)
+        stats->queue_bytes += 16ull * primary + 64ull * c[0];
         for(int b = 1; b <= p->max_depth; b++)
         {
             stats->rays_bounce += c[b - 1];
-            stats->queue_bytes += 64ull * c[b - 1] + 64ull * c[b];
+            stats->queue_bytes += (32ull + 16ull + 64ull) * c[b - 1] + 64ull * c[b];
         }
+        cudaEvent_t *ev = &sx.events[(size_t)i * evPerPass];
         float ms = 0;
-        CU(cudaEventElapsedTime(&ms, sx.events[3 * i], sx.events[3 * i + 1]));
+        CU(cudaEventElapsedTime(&ms, ev[0], ev[1]));
+        stats->ms_trace_primary += ms;
+        CU(cudaEventElapsedTime(&ms, ev[0], ev[2]));
         stats->ms_primary += ms;
-        CU(cudaEventElapsedTime(&ms, sx.events[3 * i + 1], sx.events[3 * i + 2]));
+        CU(cudaEventElapsedTime(&ms, ev[2], ev[evPerPass - 1]));
         stats->ms_bounce += ms;
+        for(int b = 1; b <= p->max_depth; b++)
+        {
+            CU(cudaEventElapsedTime(&ms, ev[2 * b], ev[1 + 2 * b]));
+            stats->ms_trace_bounce += ms;
+        }
     }
     stats->rays = stats->rays_primary + stats->rays_bounce;
     float total = 0;
-    CU(cudaEventElapsedTime(&total, sx.events[0], sx.events[3 * (size_t)(nPasses - 1) + 2]));
+    CU(cudaEventElapsedTime(&total, sx.events[0], sx.events[(size_t)nPasses * evPerPass - 1]));
     stats->ms_total = total;
     return PTB_OK;
 }

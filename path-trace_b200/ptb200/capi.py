@@ -69,7 +69,7 @@ class PtbStats(C.Structure):
     _fields_ = [
         ("paths", C.c_uint64), ("rays", C.c_uint64), ("launches", C.c_uint64), ("queue_bytes", C.c_uint64),
         ("ms_total", C.c_float), ("ms_primary", C.c_float), ("ms_bounce", C.c_float), ("ms_resolve", C.c_float),
-        ("rays_primary", C.c_uint64), ("rays_bounce", C.c_uint64),
+        ("rays_primary", C.c_uint64), ("rays_bounce", C.c_uint64), ("ms_trace_primary", C.c_float), ("ms_trace_bounce", C.c_float),
     ]
 
     def as_dict(self):
