@@ -66,6 +66,20 @@ enum
     FA_INTERSECTION = 3
 };
 #define PTB_FAST_THREADS 128
+// out-of-line or inline slow paths (measured on B200)
+#ifndef PTB_SLOW_CALLS
+#define PTB_SLOW_CALLS 0 /* bit 0: fastMerge out of line, bit 1: fastLeafHit / fastOpSlow out of line; 0 (all inline) measured fastest: C5 8.05 vs 6.87 Grays/s with 3 */
+#endif
+#if PTB_SLOW_CALLS & 1
+#define PTB_MERGE_FN static __device__ __noinline__
+#else
+#define PTB_MERGE_FN __device__ __forceinline__
+#endif
+#if PTB_SLOW_CALLS & 2
+#define PTB_SLOW_FN static __device__ __noinline__
+#else
+#define PTB_SLOW_FN __device__ __forceinline__
+#endif
 #define PTB_FAST_MAX_POST 9
 #define PTB_FAST_MAX_STACK 32
 
@@ -170,7 +184,7 @@ struct FastState
 
 // Real merge of the two top NON-EMPTY lists A = [a0, b0), B = [b0, top); returns the new top.
 // One out-of-line copy of the three state machines, everything passed by value (registers).
-static __device__ __noinline__ int fastMerge(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t op, int a0, int b0, int top)
+PTB_MERGE_FN int fastMerge(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t op, int a0, int b0, int top)
 {
     FastPool pool;
     pool.base = poolBase, pool.cap = cap, pool.ovf = ovf, pool.ovfStride = ovfStride;
@@ -214,7 +228,7 @@ static __device__ __noinline__ int fastMerge(uint32_t poolBase, int cap, float *
 //
 // Operator on the two top entries (ab: bit 1 = A, bit 0 = B) for lanes that need pool work.
 // Returns {result bit, top, sp}.
-static __device__ __noinline__ uint3 fastOpSlow(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t op, uint32_t ab, int top, uint32_t sp)
+PTB_SLOW_FN uint3 fastOpSlow(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t op, uint32_t ab, int top, uint32_t sp)
 {
     const uint32_t W = 4u * PTB_FAST_THREADS;
     if(ab == 3u)
@@ -252,7 +266,7 @@ __device__ __forceinline__ void fastOp(const FastPool &pool, uint32_t op, FastSt
 
 // A leaf that produced a span: push it, or combine it with the list below per `action`.
 // Returns {bits, top, sp}.
-static __device__ __noinline__ uint3 fastLeafHit(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t action, float t0, float t1, uint32_t tags,
+PTB_SLOW_FN uint3 fastLeafHit(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t action, float t0, float t1, uint32_t tags,
                                                  uint32_t bits, int top, uint32_t sp)
 {
     const uint32_t W = 4u * PTB_FAST_THREADS;

@@ -284,7 +284,8 @@ __device__ __forceinline__ void queueLoad(const RayQueue &q, unsigned idx, PathS
 // again by the primary shade kernel (regenerating is cheaper than a 64-byte round trip to HBM).
 __device__ __forceinline__ void cameraSample(const RenderPass &pass, unsigned nPix, unsigned long long i, PathState &ps)
 {
-    unsigned s = (unsigned)(i / nPix), p = (unsigned)(i % nPix);
+    const unsigned i32 = (unsigned)i; // the queue capacity check keeps pixels x samples per pass below 2^32
+    unsigned s = i32 / nPix, p = i32 - s * nPix;
     int px = pass.x0 + (int)(p % (unsigned)pass.rw), py = pass.y0 + (int)(p / (unsigned)pass.rw);
     ps.pixel = (unsigned)py * (unsigned)pass.width + (unsigned)px;
     ps.sample = (unsigned)(pass.sampleBase + (int)s * pass.sampleStride);
