@@ -410,9 +410,13 @@ __global__ void __launch_bounds__(PTB_SHADE_THREADS) shadeKernel(DevScene sc, Re
     const unsigned nPix = (unsigned)pass.rw * (unsigned)pass.rh;
     const unsigned long long total = PRIMARY ? (unsigned long long)nPix * (unsigned)pass.samplesThisPass : (unsigned long long)*inCount;
     const unsigned long long stride = (unsigned long long)gridDim.x * PTB_SHADE_THREADS;
+    __shared__ float4 stageAll[PTB_SHADE_THREADS / 32][4][64];
+    float4(*stage)[64] = stageAll[threadIdx.x >> 5];
+    const unsigned lane = threadIdx.x & 31u;
+    unsigned staged = 0; // warp-uniform: records waiting in this warp's staging buffer (< 32 between trips)
     for(unsigned long long base = (unsigned long long)blockIdx.x * PTB_SHADE_THREADS + (threadIdx.x & ~31u); base < total; base += stride)
     {
-        unsigned long long i = base + (threadIdx.x & 31u);
+        unsigned long long i = base + lane;
         bool alive = false;
         PathState ps;
         if(i < total)
@@ -442,18 +446,46 @@ __global__ void __launch_bounds__(PTB_SHADE_THREADS) shadeKernel(DevScene sc, Re
             }
             accumulate(accum, ps.pixel, rad, alive ? 0.f : 1.f);
         }
-        unsigned mask = __ballot_sync(0xFFFFFFFFu, alive);
-        if(mask)
+        // survivors go to the warp's staging buffer in shared memory; full groups of 32 are flushed
+        // with ONE atomic on the queue counter and four fully coalesced 512-byte stores.  (ncu: with
+        // one atomic per warp iteration 20 % of the kernel's stall samples sat on its return value.)
+        const unsigned mask = __ballot_sync(0xFFFFFFFFu, alive);
+        if(alive)
         {
-            unsigned lane = threadIdx.x & 31u;
-            int leader = __ffs(mask) - 1;
-            unsigned slot = 0;
-            if((int)lane == leader)
-                slot = atomicAdd(outCount, (unsigned)__popc(mask));
-            slot = __shfl_sync(0xFFFFFFFFu, slot, leader);
-            if(alive)
-                queueStore(out, slot + __popc(mask & ((1u << lane) - 1u)), ps);
+            unsigned at = staged + __popc(mask & ((1u << lane) - 1u));
+            stage[0][at] = make_float4(ps.o.x, ps.o.y, ps.o.z, __uint_as_float(ps.pixel));
+            stage[1][at] = make_float4(ps.d.x, ps.d.y, ps.d.z, ps.strength);
+            stage[2][at] = make_float4(ps.thr.x, ps.thr.y, ps.thr.z, __uint_as_float(ps.sample));
+            stage[3][at] = make_float4(__uint_as_float(ps.depth), __uint_as_float(ps.rngBlock), 0.f, 0.f);
         }
+        staged += __popc(mask);
+        __syncwarp();
+        if(staged >= 32u)
+        {
+            unsigned slot = 0;
+            if(lane == 0u)
+                slot = atomicAdd(outCount, 32u);
+            float4 a = stage[0][lane], b = stage[1][lane], c = stage[2][lane], e = stage[3][lane];
+            slot = __shfl_sync(0xFFFFFFFFu, slot, 0) + lane;
+            out.q0[slot] = a, out.q1[slot] = b, out.q2[slot] = c, out.q3[slot] = e;
+            staged -= 32u;
+            __syncwarp();
+            if(lane < staged)
+            { // at most 31 left: move them to the front
+                a = stage[0][32u + lane], b = stage[1][32u + lane], c = stage[2][32u + lane], e = stage[3][32u + lane];
+                stage[0][lane] = a, stage[1][lane] = b, stage[2][lane] = c, stage[3][lane] = e;
+            }
+            __syncwarp();
+        }
+    }
+    if(staged)
+    {
+        unsigned slot = 0;
+        if(lane == 0u)
+            slot = atomicAdd(outCount, staged);
+        slot = __shfl_sync(0xFFFFFFFFu, slot, 0) + lane;
+        if(lane < staged)
+            out.q0[slot] = stage[0][lane], out.q1[slot] = stage[1][lane], out.q2[slot] = stage[2][lane], out.q3[slot] = stage[3][lane];
     }
 }
 
