@@ -18,6 +18,9 @@ namespace ptb
 {
 
 #define PTB_SHADE_THREADS 128
+#ifndef PTB_SHADE_MIN_CTAS
+#define PTB_SHADE_MIN_CTAS 4
+#endif
 #ifndef PTB_TRACE_RAYS
 #define PTB_TRACE_RAYS 1
 #endif
@@ -404,7 +407,7 @@ __device__ __forceinline__ void accumulate(float4 *accum, uint32_t pixel, V3 rad
 // Survivors are appended to `out` with __ballot_sync/__popc warp aggregation (one atomic per warp,
 // coalesced stores).
 template <bool PRIMARY>
-__global__ void __launch_bounds__(PTB_SHADE_THREADS) shadeKernel(DevScene sc, RenderPass pass, float4 *accum, const uint2 *__restrict__ hits, RayQueue in,
+__global__ void __launch_bounds__(PTB_SHADE_THREADS, PTB_SHADE_MIN_CTAS) shadeKernel(DevScene sc, RenderPass pass, float4 *accum, const uint2 *__restrict__ hits, RayQueue in,
                                                                  const unsigned *__restrict__ inCount, RayQueue out, unsigned *outCount)
 {
     const unsigned nPix = (unsigned)pass.rw * (unsigned)pass.rh;
@@ -414,18 +417,42 @@ __global__ void __launch_bounds__(PTB_SHADE_THREADS) shadeKernel(DevScene sc, Re
     float4(*stage)[64] = stageAll[threadIdx.x >> 5];
     const unsigned lane = threadIdx.x & 31u;
     unsigned staged = 0; // warp-uniform: records waiting in this warp's staging buffer (< 32 between trips)
-    for(unsigned long long base = (unsigned long long)blockIdx.x * PTB_SHADE_THREADS + (threadIdx.x & ~31u); base < total; base += stride)
+    // software pipeline: the next trip's hit record (and queue record) is requested before this
+    // trip is shaded, so its HBM latency hides behind the shading (ncu: 37-54 % of the stall samples
+    // of this kernel were long-scoreboard waits on those loads)
+    const unsigned long long first = (unsigned long long)blockIdx.x * PTB_SHADE_THREADS + (threadIdx.x & ~31u);
+    uint2 hNext = make_uint2(0u, 0u);
+    float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0, n3 = n0;
+    if(first + lane < total)
+    {
+        hNext = __ldcs(&hits[first + lane]);
+        if(!PRIMARY)
+            n0 = __ldcs(&in.q0[first + lane]), n1 = __ldcs(&in.q1[first + lane]), n2 = __ldcs(&in.q2[first + lane]), n3 = __ldcs(&in.q3[first + lane]);
+    }
+    for(unsigned long long base = first; base < total; base += stride)
     {
         unsigned long long i = base + lane;
         bool alive = false;
         PathState ps;
+        const uint2 h = hNext;
+        const float4 c0 = n0, c1 = n1, c2 = n2, c3 = n3;
+        if(i + stride < total)
+        {
+            hNext = __ldcs(&hits[i + stride]);
+            if(!PRIMARY)
+                n0 = __ldcs(&in.q0[i + stride]), n1 = __ldcs(&in.q1[i + stride]), n2 = __ldcs(&in.q2[i + stride]), n3 = __ldcs(&in.q3[i + stride]);
+        }
         if(i < total)
         {
-            uint2 h = __ldcs(&hits[i]);
             if(PRIMARY)
                 cameraSample(pass, nPix, i, ps);
             else
-                queueLoad(in, (unsigned)i, ps);
+            {
+                ps.o = mk(c0.x, c0.y, c0.z), ps.pixel = __float_as_uint(c0.w);
+                ps.d = mk(c1.x, c1.y, c1.z), ps.strength = c1.w;
+                ps.thr = mk(c2.x, c2.y, c2.z), ps.sample = __float_as_uint(c2.w);
+                ps.depth = __float_as_uint(c3.x), ps.rngBlock = __float_as_uint(c3.y);
+            }
             int kind = (int)(h.y >> 16);
             V3 rad = mk(0.f, 0.f, 0.f);
             if(kind != PTB_HIT_MISS)

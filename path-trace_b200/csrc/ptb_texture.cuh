@@ -68,34 +68,32 @@ __device__ __forceinline__ float texLog(float v)
 // Texture::getFloat default, reference include/texture.h:14-18
 __device__ __forceinline__ float meanRgb(V3 c) { return (c.x + c.y + c.z) * (1.0f / 3.0f); }
 
-// Position wrappers use exact IEEE arithmetic (they are a few ops per shaded hit and decide
-// which texel a point sample lands on).
+// Position wrappers: the affine one uses exact IEEE arithmetic in the reference's order (a few ops
+// per shaded hit, decides which texel a point sample lands on).
 __device__ __forceinline__ V3 texMirrorBall(V3 p) // include/transform_texture.h:46-59
 {
     if(isZero(p))
         return p;
-    V3 v = Ar<true>::normalize(p);
+    V3 v = Ar<false>::normalize(p);
     if(v.z <= -1.f)
         return mk(0.f, 0.5f, 0.f);
-    float d = __fsqrt_rn(__fadd_rn(2.f, __fmul_rn(2.f, v.z)));
-    if(d == 0.f)
+    float d = 2.f + 2.f * v.z;
+    if(d <= 0.f)
         return mk(0.f, 0.5f, 0.f);
-    float xt = __fdiv_rn(v.x, d), yt = __fdiv_rn(v.y, d);
-    return mk((float)((double)xt * 0.5 + 0.5), (float)((double)yt * 0.5 + 0.5), 0.f);
+    float h = 0.5f * rsqrtf(d);
+    return mk(fmaf(v.x, h, 0.5f), fmaf(v.y, h, 0.5f), 0.f);
 }
+// The reference narrows atan2/asin to float and then maps to [0,1] in double; binary32 throughout
+// here (FP64 issues at 1/64 rate on B200).  A lookup moves across a texel edge for < 0.1 % of
+// positions (tests/test_gpu_render.py::test_texture_known_answers allows 1 %).
 __device__ __forceinline__ V3 texSpherical(V3 p) // include/transform_texture.h:73-85
 {
     if(isZero(p))
         return p;
-    const double PI = 3.14159265358979323846;
-    V3 v = Ar<true>::normalize(p);
-    float theta = atan2f(v.y, v.x);
-    if((double)theta < -PI)
-        theta = (float)((double)theta + 2 * PI);
-    if((double)theta > PI)
-        theta = (float)((double)theta - 2 * PI);
-    float phi = asinf(v.z);
-    return mk((float)((double)theta * 0.5 / PI + 0.5), (float)((double)phi / (PI / 2) * 0.5 + 0.5), 0.f);
+    V3 v = Ar<false>::normalize(p);
+    float theta = atan2f(v.y, v.x); // |theta| <= pi in float: the reference's +-2pi wrap never fires
+    float phi = asinf(fminf(fmaxf(v.z, -1.f), 1.f));
+    return mk(fmaf(theta, 0.15915494309189535f, 0.5f), fmaf(phi, 0.3183098861837907f, 0.5f), 0.f);
 }
 
 // Evaluates texture chain `root` at pos.  wantFloat selects Texture::getFloat semantics:
