@@ -230,78 +230,115 @@ extern "C" int ptb200_device_count(void)
     return n;
 }
 
+// ---- fast-program compiler ------------------------------------------------------------------------
+// Item of the postfix sequence the fast stream is emitted from.
+struct FastItem
+{
+    int kind;  // PTB_OP_*
+    int prim;  // PUSH_PRIM: the primitive
+    int clusterEnd; // first leaf of a plane cluster: sequence index of the Union that completes it, else -1
+};
+
 // Compiles the (validated) postfix program for the fast evaluator, ptb_csg_fast.cuh: chains folded
 // into one matrix per leaf in double precision, planes moved to world space, the operator after a
-// leaf stored as the leaf's action, further operators packed behind it, and a SKIP word before the
-// right operand of every Difference / Intersection.
-static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out)
+// leaf stored as the leaf's action, further operators packed behind it, a SKIP word before the right
+// operand of every Difference / Intersection, and a guarded CLUSTER record in front of every maximal
+// subtree that is a Union of planes only.
+//
+// Plane clusters.  Every plane yields one half-line, (-inf, t] or [t, +inf).  When every lower end lies
+// strictly below every upper start, UnionSpanIterator (src/union.cpp:84-134) reduces any tree of such
+// half-lines to {(-inf, max lower end], [min upper start, +inf)} whatever the tree's shape: lists of that
+// form merge into a list of that form (the two lower spans tie on their start, so the right operand
+// absorbs the left and keeps the larger end, :124-133; of the two upper spans the earlier start absorbs
+// the other, :113-123).  The device folds that in registers and, if the whole warp is in that case, acts
+// as one leaf and jumps over the subtree's own words.  When a lower end reaches an upper start the
+// reference's result depends on the tree (an extended span is not re-merged with later spans of its own
+// list), so the warp falls through to the subtree's words, which follow the record unchanged.
+static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, int &maxStack, int &poolBound)
 {
     auto f2u = [](float f) {
         uint32_t u;
         memcpy(&u, &f, 4);
         return u;
     };
-    // where does each operand start?  skipEnd[j] = index of the Difference/Intersection whose
-    // right operand starts at postfix position j
-    std::vector<int> skipEnd(d->n_ops, -1), first;
+    std::vector<FastItem> seq;
     for(int i = 0; i < d->n_ops; i++)
     {
-        if(PTB_OP_KIND(d->ops[i]) == PTB_OP_PUSH_PRIM)
+        uint32_t kind = PTB_OP_KIND(d->ops[i]);
+        seq.push_back(FastItem{(int)kind, kind == PTB_OP_PUSH_PRIM ? (int)PTB_OP_ARG(d->ops[i]) : -1, -1});
+    }
+    { // maximal subtrees made of planes and Unions only, at least two planes
+        struct Sub
+        {
+            int first;
+            bool pure;
+        };
+        std::vector<Sub> stack, sub(seq.size());
+        for(size_t i = 0; i < seq.size(); i++)
+        {
+            if(seq[i].kind == PTB_OP_PUSH_PRIM)
+                stack.push_back(Sub{(int)i, d->prims[seq[i].prim].type == PTB_PRIM_PLANE});
+            else
+            {
+                Sub b = stack.back();
+                stack.pop_back();
+                Sub &a = stack.back();
+                a.pure = a.pure && b.pure && seq[i].kind == PTB_OP_UNION;
+            }
+            sub[i] = stack.back();
+        }
+        int covered = (int)seq.size(); // items from here on already belong to a cluster
+        for(int i = (int)seq.size() - 1; i >= 0; i--)
+            if(i < covered && seq[i].kind != PTB_OP_PUSH_PRIM && sub[i].pure && (i - sub[i].first) / 2 + 1 <= 255)
+            {
+                seq[sub[i].first].clusterEnd = i;
+                covered = sub[i].first;
+            }
+    }
+    const int nItems = (int)seq.size();
+    { // deepest operand stack and worst-case pool use (every primitive hit, nothing fused) of THIS sequence
+        std::vector<int> sizes;
+        for(int i = 0; i < nItems; i++)
+        {
+            int total = 0;
+            for(int v : sizes)
+                total += v;
+            if(seq[i].kind == PTB_OP_PUSH_PRIM)
+            {
+                sizes.push_back(1);
+                poolBound = std::max(poolBound, total + sizes.back());
+            }
+            else
+            {
+                int lb = sizes.back();
+                sizes.pop_back();
+                int la = sizes.back();
+                sizes.back() = la + lb;
+                poolBound = std::max(poolBound, total + la + lb); // merge output is appended, then moved down
+            }
+            maxStack = std::max(maxStack, (int)sizes.size());
+        }
+    }
+    // where does each operand start?  skipEnd[j] = index of the Difference/Intersection whose
+    // right operand starts at sequence position j
+    std::vector<int> skipEnd(nItems, -1), first;
+    for(int i = 0; i < nItems; i++)
+    {
+        if(seq[i].kind == PTB_OP_PUSH_PRIM)
         {
             first.push_back(i);
             continue;
         }
         int b = first.back();
         first.pop_back();
-        if(PTB_OP_KIND(d->ops[i]) != PTB_OP_UNION)
+        if(seq[i].kind != PTB_OP_UNION)
             skipEnd[b] = i;
     }
-    std::vector<size_t> skipWord(d->n_ops, 0); // SKIP word to patch when op i has been emitted
-    size_t header = 0; // word that can still take operators
-    bool sealed = true, freshLeaf = false;
-    for(int i = 0; i < d->n_ops; i++)
-    {
-        uint32_t op = d->ops[i], kind = PTB_OP_KIND(op);
-        if(kind != PTB_OP_PUSH_PRIM)
-        {
-            uint32_t code = kind == PTB_OP_UNION ? 0u : kind == PTB_OP_DIFFERENCE ? 1u : 2u;
-            if(freshLeaf && !sealed)
-            {
-                out[header].x = (out[header].x & ~FH_MISS_SHIFT) | ((code + FA_UNION) << 4); // the leaf's action
-                if(code == 2u)
-                    out[header].x |= FH_TAIL; // a missed leaf under Intersection drops the list below
-            }
-            else
-            {
-                uint32_t n = sealed ? PTB_FAST_MAX_POST : (out[header].x >> 8) & 15u;
-                if(n >= PTB_FAST_MAX_POST)
-                {
-                    out.push_back(make_uint4(FK_OPS, 0, 0, 0));
-                    header = out.size() - 1;
-                    sealed = false;
-                    n = 0;
-                }
-                out[header].x |= code << (12 + 2 * n);
-                out[header].x = (out[header].x & ~0xF00u) | ((n + 1) << 8) | FH_TAIL;
-            }
-            freshLeaf = false;
-            if(kind != PTB_OP_UNION)
-            { // the right operand ends here: close the skipped region
-                size_t w = skipWord[i];
-                out[w].y = (uint32_t)(out.size() - (w + 1));
-                sealed = true;
-            }
-            continue;
-        }
-        if(skipEnd[i] >= 0)
-        {
-            out.push_back(make_uint4(FK_SKIP, 0, 0, 0));
-            skipWord[skipEnd[i]] = out.size() - 1;
-        }
-        uint32_t prim = PTB_OP_ARG(op);
-        const PtbPrim &p = d->prims[prim];
-        // M = M_k ... M_1 (chain_xf lists the outermost wrapper, applied first, first)
-        double M[3][4] = {{1, 0, 0, 0}, {0, 1, 0, 0}, {0, 0, 1, 0}};
+    // world -> object matrix of a primitive: M = M_k ... M_1 (chain_xf lists the outermost wrapper,
+    // applied first, first)
+    auto foldChain = [&](const PtbPrim &p, double M[3][4]) {
+        double I[3][4] = {{1, 0, 0, 0}, {0, 1, 0, 0}, {0, 0, 1, 0}};
+        memcpy(M, I, sizeof(I));
         int nchain = p.chain >= 0 ? d->chains[p.chain].count : 0;
         for(int k = 0; k < nchain; k++)
         {
@@ -315,16 +352,112 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out)
                         v += (double)m[4 * r + j] * M[j][c];
                     N[r][c] = v;
                 }
-            memcpy(M, N, sizeof(M));
+            memcpy(M, N, sizeof(N));
         }
-        uint32_t tag = prim << 1, tags = tag | (tag << 16);
+        return nchain;
+    };
+    auto worldPlane = [&](const PtbPrim &p) { // n' = M^T n, D' = D + n.t
+        double M[3][4];
+        foldChain(p, M);
+        double n[3], D = p.p[3];
+        for(int j = 0; j < 3; j++)
+            n[j] = (double)p.p[0] * M[0][j] + (double)p.p[1] * M[1][j] + (double)p.p[2] * M[2][j];
+        D += (double)p.p[0] * M[0][3] + (double)p.p[1] * M[1][3] + (double)p.p[2] * M[2][3];
+        return make_uint4(f2u((float)n[0]), f2u((float)n[1]), f2u((float)n[2]), f2u((float)D));
+    };
+    auto tagsOf = [](int prim) {
+        uint32_t tag = (uint32_t)prim << 1;
+        return tag | (tag << 16);
+    };
+    std::vector<size_t> skipWord(nItems, 0); // SKIP word to patch when item i has been emitted
+    size_t header = 0; // word that can still take operators
+    bool sealed = true, freshLeaf = false;
+    // the open cluster record: it takes the operators that follow its subtree, exactly those the
+    // subtree's last leaf word takes
+    size_t cluster = 0, clusterWords = 0;
+    int clusterEnd = -1;
+    bool clusterOpen = false, clusterFresh = false;
+    auto addOperator = [&](size_t w, bool fresh, uint32_t code) { // to a leaf / OPS word with room
+        if(fresh)
+        {
+            out[w].x = (out[w].x & ~FH_MISS_SHIFT) | ((code + FA_UNION) << 4); // the leaf's action
+            if(code == 2u)
+                out[w].x |= FH_TAIL; // a missed leaf under Intersection drops the list below
+            return;
+        }
+        uint32_t n = (out[w].x >> 8) & 15u;
+        out[w].x |= code << (12 + 2 * n);
+        out[w].x = (out[w].x & ~0xF00u) | ((n + 1) << 8) | FH_TAIL;
+    };
+    for(int i = 0; i < nItems; i++)
+    {
+        const int kind = seq[i].kind;
+        if(kind != PTB_OP_PUSH_PRIM)
+        {
+            uint32_t code = kind == PTB_OP_UNION ? 0u : kind == PTB_OP_DIFFERENCE ? 1u : 2u;
+            bool fresh = freshLeaf && !sealed;
+            if(!fresh && (sealed || ((out[header].x >> 8) & 15u) >= PTB_FAST_MAX_POST))
+            {
+                out.push_back(make_uint4(FK_OPS, 0, 0, 0));
+                header = out.size() - 1;
+                sealed = false;
+                clusterOpen = false;
+            }
+            addOperator(header, fresh, code);
+            if(clusterOpen)
+            {
+                addOperator(cluster, clusterFresh, code);
+                clusterFresh = false;
+            }
+            freshLeaf = false;
+            if(kind != PTB_OP_UNION)
+            { // the right operand ends here: close the skipped region
+                size_t w = skipWord[i];
+                out[w].y = (uint32_t)(out.size() - (w + 1));
+                sealed = true;
+                clusterOpen = false;
+            }
+            if(i == clusterEnd)
+            { // the subtree is complete: its words end here, and what follows applies to the record too
+                out[cluster].w = (uint32_t)(out.size() - (cluster + clusterWords));
+                clusterOpen = clusterFresh = !(out[header].x & FK_CONTROL);
+                if(!clusterOpen)
+                    sealed = true; // the last Union sits in an OPS word the record jumps over
+                clusterEnd = -1;
+            }
+            continue;
+        }
+        clusterOpen = false;
+        if(skipEnd[i] >= 0)
+        {
+            out.push_back(make_uint4(FK_SKIP, 0, 0, 0));
+            skipWord[skipEnd[i]] = out.size() - 1;
+        }
+        const PtbPrim &p = d->prims[seq[i].prim];
+        if(seq[i].clusterEnd >= 0)
+        { // header {x, tags, extra planes, words to jump}, plane, then {{tags}, plane} per extra plane
+            clusterEnd = seq[i].clusterEnd;
+            cluster = out.size();
+            out.push_back(make_uint4(FK_PLANE | FH_MISS_SHIFT, tagsOf(seq[i].prim), 0, 0));
+            out.push_back(worldPlane(p));
+            for(int k = i + 1; k < clusterEnd; k++)
+                if(seq[k].kind == PTB_OP_PUSH_PRIM)
+                {
+                    out.push_back(make_uint4(tagsOf(seq[k].prim), 0, 0, 0));
+                    out.push_back(worldPlane(d->prims[seq[k].prim]));
+                    out[cluster].z++;
+                }
+            clusterWords = out.size() - cluster;
+        }
         if(p.type == PTB_PRIM_SPHERE)
         {
+            double M[3][4];
+            int nchain = foldChain(p, M);
             uint32_t negR2 = f2u(-p.p[3]);
             if(nchain == 0)
             {
                 double c0 = (double)p.p[0] * p.p[0] + (double)p.p[1] * p.p[1] + (double)p.p[2] * p.p[2] - (double)p.p[3];
-                out.push_back(make_uint4(FK_SPHERE | FH_MISS_SHIFT, tags, negR2, f2u((float)c0)));
+                out.push_back(make_uint4(FK_SPHERE | FH_MISS_SHIFT, tagsOf(seq[i].prim), negR2, f2u((float)c0)));
                 header = out.size() - 1;
                 out.push_back(make_uint4(f2u(-p.p[0]), f2u(-p.p[1]), f2u(-p.p[2]), 0));
             }
@@ -333,7 +466,7 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out)
                 double c0 = -(double)p.p[3];
                 for(int r = 0; r < 3; r++)
                     c0 += (M[r][3] - (double)p.p[r]) * (M[r][3] - (double)p.p[r]);
-                out.push_back(make_uint4(FK_SPHERE_XF | FH_MISS_SHIFT, tags, negR2, f2u((float)c0)));
+                out.push_back(make_uint4(FK_SPHERE_XF | FH_MISS_SHIFT, tagsOf(seq[i].prim), negR2, f2u((float)c0)));
                 header = out.size() - 1;
                 for(int r = 0; r < 3; r++)
                     out.push_back(make_uint4(f2u((float)M[r][0]), f2u((float)M[r][1]), f2u((float)M[r][2]), f2u((float)(M[r][3] - (double)p.p[r]))));
@@ -341,20 +474,16 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out)
         }
         else
         {
-            double n[3], D = p.p[3];
-            for(int j = 0; j < 3; j++)
-                n[j] = (double)p.p[0] * M[0][j] + (double)p.p[1] * M[1][j] + (double)p.p[2] * M[2][j];
-            D += (double)p.p[0] * M[0][3] + (double)p.p[1] * M[1][3] + (double)p.p[2] * M[2][3];
-            out.push_back(make_uint4(FK_PLANE | FH_MISS_SHIFT, tags, 0, 0));
+            out.push_back(make_uint4(FK_PLANE | FH_MISS_SHIFT, tagsOf(seq[i].prim), 0, 0));
             header = out.size() - 1;
-            out.push_back(make_uint4(f2u((float)n[0]), f2u((float)n[1]), f2u((float)n[2]), f2u((float)D)));
+            out.push_back(worldPlane(p));
         }
         sealed = false;
         freshLeaf = true;
     }
     out.push_back(make_uint4(FK_END, 0, 0, 0));
     // flag union-only tails, then pairs of consecutive transformed spheres (see ptb_csg_fast.cuh)
-    auto recordLength = [&](size_t w) { return (out[w].x & FK_SPHERE_XF) ? 4u : (out[w].x & (FK_PLANE | FK_SPHERE)) ? 2u : 1u; };
+    auto recordLength = [&](size_t w) { return (out[w].x & FK_SPHERE_XF) ? 4u : (out[w].x & FK_PLANE) ? 2u + 2u * out[w].z : (out[w].x & FK_SPHERE) ? 2u : 1u; };
     for(size_t w = 0; w < out.size(); w += recordLength(w))
     {
         uint32_t x = out[w].x, n = (x >> 8) & 15u;
@@ -478,13 +607,13 @@ static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s)
     }
     if(sizes.size() != 1)
         return fail(PTB_EINVAL, "CSG program does not leave exactly one object on the stack");
+    std::vector<uint4> fast;
+    compileFastProgram(d, fast, maxStack, poolBound);
     if(maxStack > PTB_FAST_MAX_STACK)
         return fail(PTB_EINVAL, "CSG tree needs more than 32 pending operands (right-deep nesting); rebalance it");
     if(poolBound > 65535)
         return fail(PTB_EINVAL, "scene too large for 16-bit span-pool offsets");
     prog.push_back(make_uint4(DK_END, 0, 0, 0));
-    std::vector<uint4> fast;
-    compileFastProgram(d, fast);
 
     std::vector<float4> geo(d->n_prims);
     std::vector<int4> meta(d->n_prims);

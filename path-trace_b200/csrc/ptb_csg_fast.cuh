@@ -47,7 +47,7 @@ extern __shared__ uint4 ptbSmem[];
 enum
 {
     FK_SPHERE_XF = 1, // header {x, tags, -r^2, 0}, 3 rows of the folded matrix
-    FK_PLANE = 2,     // header {x, tags, 0, 0}, float4 (n.xyz, D) in world space
+    FK_PLANE = 2,     // header {x, tags, extra planes k, words to jump}, float4 (n.xyz, D) in world space, then k x {{tags}, plane}
     FK_SPHERE = 4,    // header {x, tags, -r^2, 0}, float4 (-c.xyz, 0)
     FK_CONTROL = 8,
     FK_END = 8,              // control sub-kind 0
@@ -264,34 +264,42 @@ __device__ __forceinline__ void fastOp(const FastPool &pool, uint32_t op, FastSt
     st.bits = ((st.bits >> 2) << 1) | res;
 }
 
-// A leaf that produced a span: push it, or combine it with the list below per `action`.
-// Returns {bits, top, sp}.
-PTB_SLOW_FN uint3 fastLeafHit(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t action, float t0, float t1, uint32_t tags,
-                                                 uint32_t bits, int top, uint32_t sp)
+// A leaf that produced one span (or a plane cluster that produced two, in order): push the list, or
+// combine it with the list below per `action`.  Returns {bits, top, sp}.
+PTB_SLOW_FN uint3 fastLeafHit2(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t action, bool two, const SpanRec &s, const SpanRec &s2, uint32_t bits,
+                               int top, uint32_t sp)
 {
     const uint32_t W = 4u * PTB_FAST_THREADS;
     FastPool pool;
     pool.base = poolBase, pool.cap = cap, pool.ovf = ovf, pool.ovfStride = ovfStride;
-    SpanRec s;
-    s.t0 = t0, s.t1 = t1, s.tags = tags;
+    const int n = two ? 2 : 1;
     const bool aHas = bits & 1u;
     if(action == FA_PUSH || (action == FA_UNION && !aHas))
     {
         sts32(sp, (uint32_t)top);
         pool.store(top, s);
-        return make_uint3(action == FA_PUSH ? (bits << 1) | 1u : bits | 1u, (uint32_t)(top + 1), sp + W);
+        if(two)
+            pool.store(top + 1, s2);
+        return make_uint3(action == FA_PUSH ? (bits << 1) | 1u : bits | 1u, (uint32_t)(top + n), sp + W);
     }
     if(!aHas)
         return make_uint3(bits, (uint32_t)top, sp); // {} \ B and {} n B stay empty; B is never stored
     int a0 = (int)lds32(sp - W);
     pool.store(top, s);
-    int ntop = fastMerge(poolBase, cap, ovf, ovfStride, action, a0, top, top + 1);
+    if(two)
+        pool.store(top + 1, s2);
+    int ntop = fastMerge(poolBase, cap, ovf, ovfStride, action, a0, top, top + n);
     if(ntop == a0)
         return make_uint3(bits & ~1u, (uint32_t)ntop, sp - W);
     return make_uint3(bits, (uint32_t)ntop, sp);
 }
-
-
+PTB_SLOW_FN uint3 fastLeafHit(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t action, float t0, float t1, uint32_t tags, uint32_t bits, int top,
+                              uint32_t sp)
+{
+    SpanRec s;
+    s.t0 = t0, s.t1 = t1, s.tags = tags;
+    return fastLeafHit2(poolBase, cap, ovf, ovfStride, action, false, s, s, bits, top, sp);
+}
 
 // Discriminant of one folded transformed sphere: a = |d'|^2, b = oc.d', disc = b^2 - a c
 // (src/sphere.cpp:33-38 on the ray transformed by the folded matrix).  O0: the ray starts at the
@@ -392,24 +400,90 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
             }
         }
         else if(h.x & FK_PLANE)
-        { // PlaneSpanIterator::init, src/plane.cpp:35-63, on the world-space plane
-            const uint4 u0 = PTB_PROG(1);
-            PTB_ADVANCE(2);
-            const float nx = __uint_as_float(u0.x), ny = __uint_as_float(u0.y), nz = __uint_as_float(u0.z);
+        { // PlaneSpanIterator::init, src/plane.cpp:35-63, on world-space planes.  A record holds 1 + h.z
+          // planes: one leaf (h.z == 0), or the planes of a subtree made of Unions of planes only,
+          // whose own words follow the record.  Every plane yields a half-line (-inf, t] or [t, +inf);
+          // as long as every lower end lies below every upper start their Union is, whatever the
+          // tree's shape, {(-inf, largest lower end], [smallest upper start, +inf)} (see
+          // compileFastProgram), folded here in registers and applied as ONE leaf, and the subtree's
+          // words (h.w of them) are jumped over.  If any ray of the warp is not in that case the warp
+          // runs the subtree's words instead.  Two planes alone need no such guard: two single spans
+          // that overlap always fuse into one.
+            float loEnd[R], upStart[R];
+            uint32_t loTags[R], upTags[R];
+            bool full[R];
+#pragma unroll
+            for(int r = 0; r < R; r++)
+                loEnd[r] = -3.0e38f, upStart[r] = 3.0e38f, loTags[r] = upTags[r] = 0u, full[r] = false;
+            uint32_t left = h.z, tags = h.y;
+            PTB_ADVANCE(1);
+            for(;;)
+            {
+                const uint4 u0 = PTB_PROG(0);
+                const float nx = __uint_as_float(u0.x), ny = __uint_as_float(u0.y), nz = __uint_as_float(u0.z);
+#pragma unroll
+                for(int r = 0; r < R; r++)
+                {
+                    float divisor = fmaf(d[r].x, nx, fmaf(d[r].y, ny, d[r].z * nz));
+                    float numerator = O0 ? -__uint_as_float(u0.w) : -fmaf(o[r].x, nx, fmaf(o[r].y, ny, fmaf(o[r].z, nz, __uint_as_float(u0.w))));
+                    float t = numerator * rcpApprox(divisor);
+                    bool parallel = fabsf(divisor) < PTB_EPS * PTB_EPS || !(fabsf(t) < PTB_MAX_VALUE);
+                    if(parallel)
+                    {
+                        if(fabsf(numerator) < PTB_EPS * PTB_EPS)
+                            full[r] = true, loTags[r] = upTags[r] = tags; // the ray lies in the plane: the whole line
+                    }
+                    else if(divisor < 0.0f)
+                    { // [t, +inf): the earliest start wins and brings both its tags (src/union.cpp:113-123)
+                        if(t <= upStart[r])
+                            upStart[r] = t, upTags[r] = tags;
+                    }
+                    else
+                    { // (-inf, t]: equal starts keep the later operand's start, the larger end its tag (:124-133)
+                        loTags[r] = (loTags[r] & 0xFFFF0000u) | (tags & 0xFFFFu);
+                        if(t >= loEnd[r])
+                            loEnd[r] = t, loTags[r] = (loTags[r] & 0xFFFFu) | (tags & 0xFFFF0000u);
+                    }
+                }
+                if(left == 0u)
+                {
+                    PTB_ADVANCE(1);
+                    break;
+                }
+                left--;
+                tags = PTB_PROG(1).x; // next plane: tags word, then geometry
+                PTB_ADVANCE(2);
+            }
+            if(h.z)
+            {
+                bool separate = true;
+#pragma unroll
+                for(int r = 0; r < R; r++)
+                    separate = separate && !full[r] && (h.z == 1u || loEnd[r] < upStart[r]);
+                if(!__all_sync(0xFFFFFFFFu, separate))
+                    continue; // the subtree's own words are next
+                PTB_ADVANCE(h.w);
+            }
 #pragma unroll
             for(int r = 0; r < R; r++)
             {
-                float divisor = fmaf(d[r].x, nx, fmaf(d[r].y, ny, d[r].z * nz));
-                float numerator = O0 ? -__uint_as_float(u0.w) : -fmaf(o[r].x, nx, fmaf(o[r].y, ny, fmaf(o[r].z, nz, __uint_as_float(u0.w))));
-                float t = numerator * rcpApprox(divisor);
-                bool parallel = fabsf(divisor) < PTB_EPS * PTB_EPS || !(fabsf(t) < PTB_MAX_VALUE);
-                hit[r] = !parallel || fabsf(numerator) < PTB_EPS * PTB_EPS;
-                bool lo = !parallel && divisor < 0.0f, hi = !parallel && !(divisor < 0.0f);
+                const bool hasLo = loEnd[r] > -3.0e38f, hasUp = upStart[r] < 3.0e38f;
+                SpanRec s, s2;
+                s2.t0 = upStart[r], s2.t1 = PTB_MAX_VALUE, s2.tags = upTags[r];
+                bool two = false;
+                if(full[r])
+                    s.t0 = -PTB_MAX_VALUE, s.t1 = PTB_MAX_VALUE, s.tags = upTags[r];
+                else if(loEnd[r] >= upStart[r]) // two planes only: either order gives the whole line (src/union.cpp:113-133)
+                    s.t0 = -PTB_MAX_VALUE, s.t1 = PTB_MAX_VALUE, s.tags = (loTags[r] & 0xFFFFu) | (upTags[r] & 0xFFFF0000u);
+                else if(hasLo)
+                    s.t0 = -PTB_MAX_VALUE, s.t1 = loEnd[r], s.tags = loTags[r], two = hasUp;
+                else
+                    s = s2;
+                hit[r] = full[r] || hasLo || hasUp;
                 if(hit[r])
                 {
                     FastPool pool = c.poolOf(r);
-                    uint3 q = fastLeafHit(pool.base, pool.cap, pool.ovf, pool.ovfStride, (h.x >> 4) & 3u, lo ? t : -PTB_MAX_VALUE, hi ? t : PTB_MAX_VALUE, h.y, st[r].bits,
-                                          st[r].top, st[r].sp);
+                    uint3 q = fastLeafHit2(pool.base, pool.cap, pool.ovf, pool.ovfStride, (h.x >> 4) & 3u, two, s, s2, st[r].bits, st[r].top, st[r].sp);
                     st[r].bits = q.x, st[r].top = (int)q.y, st[r].sp = q.z;
                 }
                 else
