@@ -81,6 +81,12 @@ enum
 #define PTB_SLOW_FN __device__ __forceinline__
 #endif
 #define PTB_FAST_MAX_POST 9
+#ifndef PTB_PLANE_SELECT
+#define PTB_PLANE_SELECT 0
+#endif
+#ifndef PTB_TAIL_CLOSED
+#define PTB_TAIL_CLOSED 1
+#endif
 #define PTB_FAST_MAX_STACK 32
 
 __device__ __forceinline__ uint4 lds128(uint32_t a)
@@ -428,6 +434,21 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
                     float numerator = O0 ? -__uint_as_float(u0.w) : -fmaf(o[r].x, nx, fmaf(o[r].y, ny, fmaf(o[r].z, nz, __uint_as_float(u0.w))));
                     float t = numerator * rcpApprox(divisor);
                     bool parallel = fabsf(divisor) < PTB_EPS * PTB_EPS || !(fabsf(t) < PTB_MAX_VALUE);
+#if PTB_PLANE_SELECT
+                    // selects, not branches: the cases differ from lane to lane
+                    const bool inPlane = parallel && fabsf(numerator) < PTB_EPS * PTB_EPS; // the ray lies in the plane: the whole line
+                    const bool upper = !parallel && divisor < 0.0f, lower = !parallel && !(divisor < 0.0f);
+                    // [t, +inf): the earliest start wins and brings both its tags (src/union.cpp:113-123)
+                    const bool newStart = (upper && t <= upStart[r]) || inPlane;
+                    // (-inf, t]: equal starts keep the later operand's start, the larger end its tag (:124-133)
+                    const bool newEnd = (lower && t >= loEnd[r]) || inPlane;
+                    full[r] = full[r] || inPlane;
+                    upStart[r] = newStart && !inPlane ? t : upStart[r];
+                    upTags[r] = newStart ? tags : upTags[r];
+                    loTags[r] = lower || inPlane ? (loTags[r] & 0xFFFF0000u) | (tags & 0xFFFFu) : loTags[r];
+                    loEnd[r] = newEnd && !inPlane ? t : loEnd[r];
+                    loTags[r] = newEnd ? (loTags[r] & 0xFFFFu) | (tags & 0xFFFF0000u) : loTags[r];
+#else
                     if(parallel)
                     {
                         if(fabsf(numerator) < PTB_EPS * PTB_EPS)
@@ -444,6 +465,7 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
                         if(t >= loEnd[r])
                             loEnd[r] = t, loTags[r] = (loTags[r] & 0xFFFFu) | (tags & 0xFFFF0000u);
                     }
+#endif
                 }
                 if(left == 0u)
                 {
@@ -539,11 +561,17 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
             continue;
         uint32_t npost = (h.x >> 8) & 15u;
         if(h.x & FH_UNION_TAIL)
-        { // a run of Unions: bit arithmetic unless both lists have spans
-            do
-            {
+        { // a run of Unions: the lists involved collapse into one; spans move only if two of them have any
 #pragma unroll
-                for(int r = 0; r < R; r++)
+            for(int r = 0; r < R; r++)
+            {
+                const uint32_t involved = st[r].bits & ((2u << npost) - 1u);
+                if(PTB_TAIL_CLOSED && __popc(involved) <= 1)
+                {
+                    st[r].bits = ((st[r].bits >> npost) & ~1u) | (involved ? 1u : 0u);
+                    continue;
+                }
+                for(uint32_t k = npost; k; k--)
                 {
                     if((st[r].bits & 3u) == 3u)
                     {
@@ -553,7 +581,7 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
                     }
                     st[r].bits = (st[r].bits >> 1) | (st[r].bits & 1u);
                 }
-            } while(--npost);
+            }
             continue;
         }
         if(((h.x >> 4) & 3u) == FA_INTERSECTION && !(h.x & FK_CONTROL))
