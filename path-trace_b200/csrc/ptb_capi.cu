@@ -952,10 +952,10 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
     CU(sx.queues.ensure(capacity * 64 * 2));
     CU(sx.hits.ensure(capacity * sizeof(uint2)));
     uint2 *hits = (uint2 *)sx.hits.p;
-    int shadePerSm = shadeBlocksPerSm();
-    if(shadePerSm <= 0)
+    const int shadePerSm = shadeBlocksPerSm(true), shadePerSmBounce = shadeBlocksPerSm(false);
+    if(shadePerSm <= 0 || shadePerSmBounce <= 0)
         return fail(PTB_ECUDA, "shade kernel does not fit on an SM");
-    const int shadeBlocks = shadePerSm * s->smCount;
+    const int shadeBlocks = shadePerSm * s->smCount, shadeBlocksBounce = shadePerSmBounce * s->smCount;
     CU(sx.counters.ensure((size_t)nPasses * (stages + 1) * sizeof(unsigned)));
     CU(cudaMemsetAsync(sx.counters.p, 0, (size_t)nPasses * (stages + 1) * sizeof(unsigned), stream));
     RayQueue q[2];
@@ -1001,7 +1001,7 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
             launchTraceQueue(s->dev, cfg, q[(b - 1) & 1], c + (b - 1), hits, stream);
             if(timed)
                 CU(cudaEventRecord(ev[1 + 2 * b], stream));
-            launchShade(s->dev, shadeBlocks, false, pass, accum, hits, q[(b - 1) & 1], c + (b - 1), q[b & 1], c + b, stream);
+            launchShade(s->dev, shadeBlocksBounce, false, pass, accum, hits, q[(b - 1) & 1], c + (b - 1), q[b & 1], c + b, stream);
             if(timed)
                 CU(cudaEventRecord(ev[2 + 2 * b], stream));
         }

@@ -18,8 +18,13 @@ namespace ptb
 {
 
 #define PTB_SHADE_THREADS 128
+// CTAs per SM the shade kernels are compiled for: camera hits are coherent and want registers (128),
+// bounce hits are scattered and want warps to hide their gathers (80 registers)
 #ifndef PTB_SHADE_MIN_CTAS
 #define PTB_SHADE_MIN_CTAS 4
+#endif
+#ifndef PTB_SHADE_MIN_CTAS_BOUNCE
+#define PTB_SHADE_MIN_CTAS_BOUNCE 6
 #endif
 #ifndef PTB_TRACE_RAYS
 #define PTB_TRACE_RAYS 1
@@ -407,7 +412,7 @@ __device__ __forceinline__ void accumulate(float4 *accum, uint32_t pixel, V3 rad
 // Survivors are appended to `out` with __ballot_sync/__popc warp aggregation (one atomic per warp,
 // coalesced stores).
 template <bool PRIMARY>
-__global__ void __launch_bounds__(PTB_SHADE_THREADS, PTB_SHADE_MIN_CTAS) shadeKernel(DevScene sc, RenderPass pass, float4 *accum, const uint2 *__restrict__ hits, RayQueue in,
+__global__ void __launch_bounds__(PTB_SHADE_THREADS, PRIMARY ? PTB_SHADE_MIN_CTAS : PTB_SHADE_MIN_CTAS_BOUNCE) shadeKernel(DevScene sc, RenderPass pass, float4 *accum, const uint2 *__restrict__ hits, RayQueue in,
                                                                  const unsigned *__restrict__ inCount, RayQueue out, unsigned *outCount)
 {
     const unsigned nPix = (unsigned)pass.rw * (unsigned)pass.rh;
@@ -550,10 +555,11 @@ void launchShade(const DevScene &sc, int blocks, bool primary, const RenderPass 
     else
         shadeKernel<false><<<blocks, PTB_SHADE_THREADS, 0, stream>>>(sc, pass, accum, hits, in, inCount, out, outCount);
 }
-int shadeBlocksPerSm()
+int shadeBlocksPerSm(bool primary)
 {
     int n = 0;
-    if(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<false>, PTB_SHADE_THREADS, 0) != cudaSuccess)
+    if((primary ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<true>, PTB_SHADE_THREADS, 0)
+                : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<false>, PTB_SHADE_THREADS, 0)) != cudaSuccess)
     {
         cudaGetLastError();
         return 0;

@@ -51,7 +51,7 @@ void launchTraceQueue(const DevScene &sc, const CsgConfig &cfg, RayQueue in, con
 // path state regenerated from the sample index; else read from `in` (*inCount entries).
 void launchShade(const DevScene &sc, int blocks, bool primary, const RenderPass &pass, float4 *accum, const uint2 *hits, RayQueue in, const unsigned *inCount, RayQueue out,
                  unsigned *outCount, cudaStream_t stream);
-int shadeBlocksPerSm();
+int shadeBlocksPerSm(bool primary);
 void launchResolve(const float4 *accum, float4 *rgba, size_t nPixels, cudaStream_t stream);
 void launchTextureEval(const DevScene &sc, int root, const float *pos, size_t n, float *rgb, float *f, uint32_t flags, cudaStream_t stream);
 void launchScatterSample(const float *normal, const float *refl, float scatter, size_t n, uint64_t seed, uint32_t flags, float *dirs, cudaStream_t stream);
