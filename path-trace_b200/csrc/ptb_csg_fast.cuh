@@ -270,43 +270,6 @@ __device__ __forceinline__ void fastOp(const FastPool &pool, uint32_t op, FastSt
     st.bits = ((st.bits >> 2) << 1) | res;
 }
 
-// A leaf that produced one span (or a plane cluster that produced two, in order): push the list, or
-// combine it with the list below per `action`.  Returns {bits, top, sp}.
-PTB_SLOW_FN uint3 fastLeafHit2(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t action, bool two, const SpanRec &s, const SpanRec &s2, uint32_t bits,
-                               int top, uint32_t sp)
-{
-    const uint32_t W = 4u * PTB_FAST_THREADS;
-    FastPool pool;
-    pool.base = poolBase, pool.cap = cap, pool.ovf = ovf, pool.ovfStride = ovfStride;
-    const int n = two ? 2 : 1;
-    const bool aHas = bits & 1u;
-    if(action == FA_PUSH || (action == FA_UNION && !aHas))
-    {
-        sts32(sp, (uint32_t)top);
-        pool.store(top, s);
-        if(two)
-            pool.store(top + 1, s2);
-        return make_uint3(action == FA_PUSH ? (bits << 1) | 1u : bits | 1u, (uint32_t)(top + n), sp + W);
-    }
-    if(!aHas)
-        return make_uint3(bits, (uint32_t)top, sp); // {} \ B and {} n B stay empty; B is never stored
-    int a0 = (int)lds32(sp - W);
-    pool.store(top, s);
-    if(two)
-        pool.store(top + 1, s2);
-    int ntop = fastMerge(poolBase, cap, ovf, ovfStride, action, a0, top, top + n);
-    if(ntop == a0)
-        return make_uint3(bits & ~1u, (uint32_t)ntop, sp - W);
-    return make_uint3(bits, (uint32_t)ntop, sp);
-}
-PTB_SLOW_FN uint3 fastLeafHit(uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t action, float t0, float t1, uint32_t tags, uint32_t bits, int top,
-                              uint32_t sp)
-{
-    SpanRec s;
-    s.t0 = t0, s.t1 = t1, s.tags = tags;
-    return fastLeafHit2(poolBase, cap, ovf, ovfStride, action, false, s, s, bits, top, sp);
-}
-
 // Discriminant of one folded transformed sphere: a = |d'|^2, b = oc.d', disc = b^2 - a c
 // (src/sphere.cpp:33-38 on the ray transformed by the folded matrix).  O0: the ray starts at the
 // world origin (every camera ray), so oc is the matrix translation and c is the header constant.
@@ -337,19 +300,6 @@ __device__ __forceinline__ void xfDisc(const uint4 &h, const uint4 &u0, const ui
     disc = fmaf(b, b, -(a * cc));
 }
 
-// Leaf epilogue for one ray: the common case (miss) is one shift.
-__device__ __forceinline__ void fastLeafDone(const FastPool &pool, uint32_t hx, uint32_t tags, bool hit, float a, float b, float disc, FastState &st)
-{
-    if(hit)
-    { // src/sphere.cpp:44-46
-        float s = sqrtApprox(disc), ia = rcpApprox(a);
-        uint3 q = fastLeafHit(pool.base, pool.cap, pool.ovf, pool.ovfStride, (hx >> 4) & 3u, (-b - s) * ia, (-b + s) * ia, tags, st.bits, st.top, st.sp);
-        st.bits = q.x, st.top = (int)q.y, st.sp = q.z;
-    }
-    else
-        st.bits <<= (hx >> 6) & 1u;
-}
-
 // Runs the whole program for R rays per lane, all 32 lanes of the warp together (SKIP words
 // vote).  Ray r's root span list ends up in pool r, slots [0, topOut[r]).  (R = 2 was measured
 // slower than R = 1 on B200 — occupancy beats per-thread ILP here — and is kept for experiments.)
@@ -364,46 +314,94 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
     uint32_t pc = GP ? 0u : c.prog; // GP: word index; else shared byte address
 #define PTB_PROG(i) (GP ? __ldg(gprog + pc + (i)) : lds128(pc + 16u * (i)))
 #define PTB_ADVANCE(n) (pc += GP ? (uint32_t)(n) : 16u * (uint32_t)(n))
+// The commonest trips by far, taken by the whole warp together (votes), so that the loop stays
+// converged for the SKIP votes: no ray of the warp hits the leaf, and either no operator follows it in
+// its word, or a run of Unions does that moves no spans (at most one of the lists involved has any).
+#define PTB_MISS_EXIT()                                                                                      \
+    {                                                                                                        \
+        bool anyHit = false;                                                                                 \
+        _Pragma("unroll") for(int r = 0; r < R; r++) anyHit = anyHit || hit[r];                              \
+        if(!__any_sync(0xFFFFFFFFu, anyHit))                                                                 \
+        {                                                                                                    \
+            if(!(h.x & FH_TAIL))                                                                             \
+            {                                                                                                \
+                _Pragma("unroll") for(int r = 0; r < R; r++) st[r].bits <<= (h.x >> 6) & 1u;                 \
+                continue;                                                                                    \
+            }                                                                                                \
+            if(PTB_TAIL_CLOSED && (h.x & FH_UNION_TAIL))                                                     \
+            { /* the leaf's own action is Union or Difference: a miss changes nothing */                    \
+                const uint32_t np = (h.x >> 8) & 15u, mask = (2u << np) - 1u;                                \
+                bool simple = true;                                                                          \
+                _Pragma("unroll") for(int r = 0; r < R; r++) simple = simple && __popc(st[r].bits & mask) <= 1; \
+                if(__all_sync(0xFFFFFFFFu, simple))                                                          \
+                {                                                                                            \
+                    _Pragma("unroll") for(int r = 0; r < R; r++)                                             \
+                        st[r].bits = ((st[r].bits >> np) & ~1u) | ((st[r].bits & mask) ? 1u : 0u);           \
+                    continue;                                                                                \
+                }                                                                                            \
+            }                                                                                                \
+        }                                                                                                    \
+    }
     for(;;)
     {
         uint4 h = PTB_PROG(0);
-        bool hit[R];
+        // what the leaf in this word produced: nothing, one span, or (plane clusters) two in order
+        bool hit[R], two[R];
+        float lt0[R], lt1[R], ut0[R];
+        uint32_t ltags[R], utags[R];
+#pragma unroll
+        for(int r = 0; r < R; r++)
+            ltags[r] = h.y; // (the rest is set by the branch that sets hit[r]; two[r], ut0[r], utags[r] by planes only)
         if(h.x & FK_SPHERE_XF)
         {
+            const uint4 u0 = PTB_PROG(1), u1 = PTB_PROG(2), u2 = PTB_PROG(3);
+            float a[R], b[R], e[R];
             if(h.x & FH_PAIR)
-            { // two tail-less... the first has no tail; both discriminants are computed together (ILP)
-                const uint4 u0 = PTB_PROG(1), u1 = PTB_PROG(2), u2 = PTB_PROG(3);
+            { // the next word is a transformed sphere too and this one has no tail: both discriminants
+              // are computed together (ILP).  If no ray of the warp hits the first, it is done with and
+              // the second becomes the leaf of this trip; otherwise the second waits for the next trip.
                 const uint4 g = PTB_PROG(4), v0 = PTB_PROG(5), v1 = PTB_PROG(6), v2 = PTB_PROG(7);
-                PTB_ADVANCE(8);
-                float a0[R], b0[R], e0[R], a1[R], b1[R], e1[R];
+                float a1[R], b1[R], e1[R];
+                bool any = false;
 #pragma unroll
                 for(int r = 0; r < R; r++)
                 {
-                    xfDisc<O0>(h, u0, u1, u2, o[r], d[r], a0[r], b0[r], e0[r]);
+                    xfDisc<O0>(h, u0, u1, u2, o[r], d[r], a[r], b[r], e[r]);
                     xfDisc<O0>(g, v0, v1, v2, o[r], d[r], a1[r], b1[r], e1[r]);
+                    any = any || e[r] > PTB_EPS;
                 }
-#pragma unroll
-                for(int r = 0; r < R; r++)
+                PTB_ADVANCE(4);
+                if(!__any_sync(0xFFFFFFFFu, any))
                 {
-                    fastLeafDone(c.poolOf(r), h.x, h.y, e0[r] > PTB_EPS, a0[r], b0[r], e0[r], st[r]);
-                    hit[r] = e1[r] > PTB_EPS;
-                    fastLeafDone(c.poolOf(r), g.x, g.y, hit[r], a1[r], b1[r], e1[r], st[r]);
+#pragma unroll
+                    for(int r = 0; r < R; r++)
+                    {
+                        st[r].bits <<= (h.x >> 6) & 1u; // (a leaf under Intersection has a tail: never first of a pair)
+                        a[r] = a1[r], b[r] = b1[r], e[r] = e1[r];
+                        ltags[r] = g.y;
+                    }
+                    h = g;
+                    PTB_ADVANCE(4);
                 }
-                h = g; // the second leaf's tail, if any, runs below
             }
             else
             {
-                const uint4 u0 = PTB_PROG(1), u1 = PTB_PROG(2), u2 = PTB_PROG(3);
-                PTB_ADVANCE(4);
 #pragma unroll
                 for(int r = 0; r < R; r++)
-                {
-                    float a, b, e;
-                    xfDisc<O0>(h, u0, u1, u2, o[r], d[r], a, b, e);
-                    hit[r] = e > PTB_EPS;
-                    fastLeafDone(c.poolOf(r), h.x, h.y, hit[r], a, b, e, st[r]);
-                }
+                    xfDisc<O0>(h, u0, u1, u2, o[r], d[r], a[r], b[r], e[r]);
+                PTB_ADVANCE(4);
             }
+#pragma unroll
+            for(int r = 0; r < R; r++)
+                hit[r] = e[r] > PTB_EPS;
+            PTB_MISS_EXIT();
+#pragma unroll
+            for(int r = 0; r < R; r++)
+                if(hit[r])
+                { // src/sphere.cpp:44-46
+                    float q = sqrtApprox(e[r]), ia = rcpApprox(a[r]);
+                    lt0[r] = (-b[r] - q) * ia, lt1[r] = (-b[r] + q) * ia;
+                }
         }
         else if(h.x & FK_PLANE)
         { // PlaneSpanIterator::init, src/plane.cpp:35-63, on world-space planes.  A record holds 1 + h.z
@@ -490,27 +488,20 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
             for(int r = 0; r < R; r++)
             {
                 const bool hasLo = loEnd[r] > -3.0e38f, hasUp = upStart[r] < 3.0e38f;
-                SpanRec s, s2;
-                s2.t0 = upStart[r], s2.t1 = PTB_MAX_VALUE, s2.tags = upTags[r];
-                bool two = false;
-                if(full[r])
-                    s.t0 = -PTB_MAX_VALUE, s.t1 = PTB_MAX_VALUE, s.tags = upTags[r];
-                else if(loEnd[r] >= upStart[r]) // two planes only: either order gives the whole line (src/union.cpp:113-133)
-                    s.t0 = -PTB_MAX_VALUE, s.t1 = PTB_MAX_VALUE, s.tags = (loTags[r] & 0xFFFFu) | (upTags[r] & 0xFFFF0000u);
-                else if(hasLo)
-                    s.t0 = -PTB_MAX_VALUE, s.t1 = loEnd[r], s.tags = loTags[r], two = hasUp;
-                else
-                    s = s2;
                 hit[r] = full[r] || hasLo || hasUp;
-                if(hit[r])
-                {
-                    FastPool pool = c.poolOf(r);
-                    uint3 q = fastLeafHit2(pool.base, pool.cap, pool.ovf, pool.ovfStride, (h.x >> 4) & 3u, two, s, s2, st[r].bits, st[r].top, st[r].sp);
-                    st[r].bits = q.x, st[r].top = (int)q.y, st[r].sp = q.z;
-                }
+                two[r] = false;
+                lt0[r] = -PTB_MAX_VALUE, lt1[r] = PTB_MAX_VALUE, ltags[r] = upTags[r]; // the whole line (a ray in the plane)
+                ut0[r] = upStart[r], utags[r] = upTags[r];
+                if(full[r])
+                    ;
+                else if(loEnd[r] >= upStart[r]) // two planes only: either order gives the whole line (src/union.cpp:113-133)
+                    ltags[r] = (loTags[r] & 0xFFFFu) | (upTags[r] & 0xFFFF0000u);
+                else if(hasLo)
+                    lt1[r] = loEnd[r], ltags[r] = loTags[r], two[r] = hasUp;
                 else
-                    st[r].bits <<= (h.x >> 6) & 1u;
+                    lt0[r] = upStart[r];
             }
+            PTB_MISS_EXIT();
         }
         else if(h.x & FK_SPHERE)
         {
@@ -534,8 +525,13 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
                 }
                 float e = fmaf(b, b, -(a * cc));
                 hit[r] = e > PTB_EPS;
-                fastLeafDone(c.poolOf(r), h.x, h.y, hit[r], a, b, e, st[r]);
+                if(hit[r])
+                { // src/sphere.cpp:44-46
+                    float q = sqrtApprox(e), ia = rcpApprox(a);
+                    lt0[r] = (-b - q) * ia, lt1[r] = (-b + q) * ia;
+                }
             }
+            PTB_MISS_EXIT();
         }
         else
         { // control word
@@ -553,60 +549,76 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
                     PTB_ADVANCE(h.y);
                 continue;
             }
-#pragma unroll
-            for(int r = 0; r < R; r++)
-                hit[r] = true; // an OPS word has no leaf: nothing to drop below
         }
-        if(!(h.x & FH_TAIL))
-            continue;
-        uint32_t npost = (h.x >> 8) & 15u;
-        if(h.x & FH_UNION_TAIL)
-        { // a run of Unions: the lists involved collapse into one; spans move only if two of them have any
+        // ---- the ONE place where lists are pushed and operators run (the code of the three merge
+        // state machines exists once in the kernel: the hot loop stays instruction-cache resident) ----
+        const bool isLeaf = !(h.x & FK_CONTROL);
+        const uint32_t action = (h.x >> 4) & 3u, npost = (h.x >> 8) & 15u;
+        const bool tail = (h.x & (FH_TAIL | FK_CONTROL)) != 0u, isPlane = (h.x & FK_PLANE) != 0u;
 #pragma unroll
-            for(int r = 0; r < R; r++)
+        for(int r = 0; r < R; r++)
+        {
+            if(!tail && !hit[r])
+            { // a missed leaf with nothing behind it is an empty list, or nothing at all
+                st[r].bits <<= (h.x >> 6) & 1u;
+                continue;
+            }
+            const FastPool pool = c.poolOf(r);
+            uint32_t first = 0u; // the leaf's action, if it has to run as an operator on two lists
+            if(isLeaf)
             {
-                const uint32_t involved = st[r].bits & ((2u << npost) - 1u);
-                if(PTB_TAIL_CLOSED && __popc(involved) <= 1)
+                if(!hit[r])
                 {
+                    st[r].bits <<= (h.x >> 6) & 1u; // a pushed leaf that missed is an empty list
+                    if(action == FA_INTERSECTION && (st[r].bits & 1u))
+                    { // A n {} = {}: a missed leaf drops the spans of the list below
+                        st[r].sp -= W;
+                        st[r].top = (int)lds32(st[r].sp);
+                        st[r].bits &= ~1u;
+                    }
+                }
+                else if(action <= FA_UNION || (st[r].bits & 1u))
+                { // push the leaf's list ({} \ B and {} n B stay empty: B is never stored)
+                    SpanRec s;
+                    s.t0 = lt0[r], s.t1 = lt1[r], s.tags = ltags[r];
+                    sts32(st[r].sp, (uint32_t)st[r].top);
+                    pool.store(st[r].top, s);
+                    const bool second = isPlane && two[r];
+                    if(second)
+                    {
+                        s.t0 = ut0[r], s.t1 = PTB_MAX_VALUE, s.tags = utags[r];
+                        pool.store(st[r].top + 1, s);
+                    }
+                    st[r].top += second ? 2 : 1, st[r].sp += W, st[r].bits = (st[r].bits << 1) | 1u;
+                    first = action;
+                }
+            }
+            if(first == 0u)
+            {
+                if(npost == 0u)
+                    continue;
+                const uint32_t involved = st[r].bits & ((2u << npost) - 1u);
+                if(PTB_TAIL_CLOSED && (h.x & FH_UNION_TAIL) && __popc(involved) <= 1)
+                { // a run of Unions: the lists involved collapse into one; spans move only if two of them have any
                     st[r].bits = ((st[r].bits >> npost) & ~1u) | (involved ? 1u : 0u);
                     continue;
                 }
-                for(uint32_t k = npost; k; k--)
-                {
-                    if((st[r].bits & 3u) == 3u)
-                    {
-                        FastPool pool = c.poolOf(r);
-                        uint3 q = fastOpSlow(pool.base, pool.cap, pool.ovf, pool.ovfStride, FA_UNION, 3u, st[r].top, st[r].sp);
-                        st[r].top = (int)q.y, st[r].sp = q.z;
-                    }
-                    st[r].bits = (st[r].bits >> 1) | (st[r].bits & 1u);
-                }
             }
-            continue;
-        }
-        if(((h.x >> 4) & 3u) == FA_INTERSECTION && !(h.x & FK_CONTROL))
-        { // A n {} = {}: a missed leaf drops the spans of the list below
-#pragma unroll
-            for(int r = 0; r < R; r++)
-                if(!hit[r] && (st[r].bits & 1u))
-                {
-                    st[r].sp -= W;
-                    st[r].top = (int)lds32(st[r].sp);
-                    st[r].bits &= ~1u;
-                }
-        }
-        uint32_t post = h.x >> 12;
-        while(npost)
-        {
-            const uint32_t op = (post & 3u) + FA_UNION;
-#pragma unroll
-            for(int r = 0; r < R; r++)
-                fastOp(c.poolOf(r), op, st[r]);
-            post >>= 2, npost--;
+            uint32_t ops = h.x >> 12, left = npost, op = first;
+            if(op == 0u)
+                op = (ops & 3u) + FA_UNION, ops >>= 2, left--;
+            for(;;)
+            {
+                fastOp(pool, op, st[r]);
+                if(left == 0u)
+                    break;
+                op = (ops & 3u) + FA_UNION, ops >>= 2, left--;
+            }
         }
     }
 #undef PTB_PROG
 #undef PTB_ADVANCE
+#undef PTB_MISS_EXIT
 #pragma unroll
     for(int r = 0; r < R; r++)
         topOut[r] = st[r].top;
