@@ -589,8 +589,9 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
                         s.t0 = ut0[r], s.t1 = PTB_MAX_VALUE, s.tags = utags[r];
                         pool.store(st[r].top + 1, s);
                     }
-                    st[r].top += second ? 2 : 1, st[r].sp += W, st[r].bits = (st[r].bits << 1) | 1u;
-                    first = action;
+                    const bool replaces = action == FA_UNION && !(st[r].bits & 1u); // {} u B = B: B takes the empty list's entry
+                    st[r].top += second ? 2 : 1, st[r].sp += W, st[r].bits = replaces ? st[r].bits | 1u : (st[r].bits << 1) | 1u;
+                    first = replaces ? 0u : action;
                 }
             }
             if(first == 0u)
