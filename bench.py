@@ -226,8 +226,12 @@ def run_ours(args):
     e2e_steps = max(1, min(args.steps, 2))
     host_np = host_image.numpy()
 
+    e2e_parts = [0.0, 0.0, 0.0]  # scene create, render + download, destroy (host clock, rank 0's own)
+
     def e2e_step():
+        t_a = time.perf_counter()
         sc2 = device.DeviceScene(flat)
+        t_b = time.perf_counter()
         if world_size == 1:
             sc2.render(params, host_np)
         else:
@@ -238,9 +242,14 @@ def run_ours(args):
                 device.resolve(accum, rgba, stream)
                 host_image.copy_(rgba, non_blocking=True)
         torch.cuda.synchronize()
+        t_c = time.perf_counter()
         sc2.close()
+        t_d = time.perf_counter()
+        for k, v in enumerate((t_b - t_a, t_c - t_b, t_d - t_c)):
+            e2e_parts[k] += v * 1e3 / e2e_steps
 
     e2e_step()
+    e2e_parts[:] = [0.0, 0.0, 0.0]
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
@@ -283,7 +292,7 @@ def run_ours(args):
                    "parallelism": "spp-sharded x%d + NCCL sum-reduce" % world_size if world_size > 1 else "1 GPU",
                    "l2": "accumulation buffer (133 MB) is rewritten and the ray queues (GBs) stream through HBM every step: working set >> 126 MB L2"},
         "mpaths_per_s": paths / (ms_per_step * 1e-3) / 1e6, "rays_per_path": rays / paths,
-        "e2e": {"value": rays / (e2e_ms.item() * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms.item(), "h2d_bytes_per_step": h2d,
+        "e2e": {"value": rays / (e2e_ms.item() * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms.item(), "parts_ms": {"scene_create": e2e_parts[0], "render_and_download": e2e_parts[1], "destroy": e2e_parts[2]}, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": width * height * 16, "what": "ptb200_scene_create (uploads scene + images) + ptb200_render into a host buffer + destroy, per step"},
         "gpu_launches": int(launches / world_size) * args.steps + args.steps * (1 if rank == 0 else 0),
         "clocks": sampler.summary(),

@@ -203,6 +203,11 @@ typedef struct PtbStats {
 const char *ptb200_last_error(void);
 int ptb200_abi_version(void);
 int ptb200_device_count(void);
+/* Device scratch (ray queues, hit records, accumulation buffers: GBs at 4K) is cached by the library
+ * when a scene is destroyed and reused by the next one, because cudaMalloc/cudaFree of such blocks
+ * cost up to seconds.  ptb200_trim() gives the cached blocks back to the driver.  (No reference
+ * counterpart: the reference allocates per RenderBlock on the heap, src/test.cpp:325-340.) */
+int ptb200_trim(void);
 
 /* Copies everything it needs (caller keeps its buffers); the scene lives on the CUDA device that
  * is current at the time of the call.  Validates the program (stack discipline, index ranges). */

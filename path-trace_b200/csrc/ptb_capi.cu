@@ -33,15 +33,62 @@ int fail(int code, const std::string &msg)
             return fail(PTB_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_));                    \
     } while(0)
 
+// Scratch blocks are cached per process instead of going back to the driver: cudaMalloc / cudaFree of
+// the multi-GB ray queues cost from milliseconds to seconds (cudaFree synchronises the device and
+// unmaps) and a renderer that creates and destroys scenes per frame would pay that every frame.
+// ptb200_trim() returns the cache to the driver; an allocation that fails trims and retries.
+struct CachedBlock
+{
+    void *p;
+    size_t bytes;
+    int device;
+};
+static std::mutex g_cacheLock;
+static std::vector<CachedBlock> g_cache;
+
+static void cacheTrim(int device)
+{ // device < 0: every device
+    std::vector<CachedBlock> drop;
+    {
+        std::lock_guard<std::mutex> g(g_cacheLock);
+        for(size_t i = 0; i < g_cache.size();)
+            if(device < 0 || g_cache[i].device == device)
+            {
+                drop.push_back(g_cache[i]);
+                g_cache[i] = g_cache.back();
+                g_cache.pop_back();
+            }
+            else
+                i++;
+    }
+    int current = 0;
+    cudaGetDevice(&current);
+    for(const CachedBlock &b : drop)
+    {
+        cudaSetDevice(b.device);
+        cudaFree(b.p);
+    }
+    cudaSetDevice(current);
+}
+
 struct DeviceBuffer
 {
     void *p = nullptr;
     size_t bytes = 0;
+    int device = 0;
     ~DeviceBuffer() { release(); }
     void release()
     {
         if(p)
-            cudaFree(p);
+        {
+            if(bytes >= (1u << 20))
+            {
+                std::lock_guard<std::mutex> g(g_cacheLock);
+                g_cache.push_back(CachedBlock{p, bytes, device});
+            }
+            else
+                cudaFree(p);
+        }
         p = nullptr, bytes = 0;
     }
     cudaError_t ensure(size_t n)
@@ -49,9 +96,34 @@ struct DeviceBuffer
         if(n <= bytes)
             return cudaSuccess;
         release();
-        cudaError_t e = cudaMalloc(&p, n);
+        cudaError_t e = cudaGetDevice(&device);
+        if(e != cudaSuccess)
+            return e;
+        { // best fit among the cached blocks of this device, at most twice the size asked for
+            std::lock_guard<std::mutex> g(g_cacheLock);
+            size_t best = g_cache.size();
+            for(size_t i = 0; i < g_cache.size(); i++)
+                if(g_cache[i].device == device && g_cache[i].bytes >= n && g_cache[i].bytes / 2 <= n && (best == g_cache.size() || g_cache[i].bytes < g_cache[best].bytes))
+                    best = i;
+            if(best != g_cache.size())
+            {
+                p = g_cache[best].p, bytes = g_cache[best].bytes;
+                g_cache[best] = g_cache.back();
+                g_cache.pop_back();
+                return cudaSuccess;
+            }
+        }
+        e = cudaMalloc(&p, n);
+        if(e != cudaSuccess)
+        {
+            cudaGetLastError();
+            cacheTrim(device);
+            e = cudaMalloc(&p, n);
+        }
         if(e == cudaSuccess)
             bytes = n;
+        else
+            p = nullptr;
         return e;
     }
 };
@@ -222,6 +294,11 @@ int validateTexture(const PtbSceneDesc *d, int root)
 // ---- scene ------------------------------------------------------------------------------------
 extern "C" const char *ptb200_last_error(void) { return g_error.c_str(); }
 extern "C" int ptb200_abi_version(void) { return PTB200_ABI_VERSION; }
+extern "C" int ptb200_trim(void)
+{
+    cacheTrim(-1);
+    return PTB_OK;
+}
 extern "C" int ptb200_device_count(void)
 {
     int n = 0;

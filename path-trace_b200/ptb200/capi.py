@@ -84,7 +84,7 @@ assert HIT_DTYPE.itemsize == 32 and SPAN_DTYPE.itemsize == 48
 
 # every symbol include/ptb200.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
-    "ptb200_last_error", "ptb200_abi_version", "ptb200_device_count", "ptb200_scene_create", "ptb200_scene_destroy", "ptb200_image_upload",
+    "ptb200_last_error", "ptb200_abi_version", "ptb200_device_count", "ptb200_trim", "ptb200_scene_create", "ptb200_scene_destroy", "ptb200_image_upload",
     "ptb200_intersect", "ptb200_intersect_device", "ptb200_texture_eval", "ptb200_render", "ptb200_render_accumulate_device", "ptb200_resolve_device",
     "ptb200_render_async", "ptb200_job_done", "ptb200_job_read", "ptb200_job_wait", "ptb200_job_destroy", "ptb200_sample_scatter", "ptb200_fp32_peak",
 ]

@@ -163,6 +163,27 @@ def test_passes_do_not_change_the_estimate():
     assert np.allclose(a, c, rtol=1e-4, atol=1e-5)
 
 
+def test_scratch_cache_survives_scene_lifetimes_and_trim():
+    """Scratch blocks are cached across scenes (include/ptb200.h: ptb200_trim): a scene created after
+    another one was destroyed renders the same image from recycled (dirty) blocks, and again after a trim."""
+    lib = capi.product()
+    flat = device.Flat(gc.render_scene(product_builder(), "c2"))
+    params = device.default_params(256, 144, 16, seed=9)
+    images = []
+    for trim in (False, False, True):
+        sc = device.DeviceScene(flat)
+        img, st = sc.render(params)
+        assert st.paths == 256 * 144 * 16
+        images.append(img)
+        sc.close()
+        if trim:
+            assert lib.ptb200_trim() == 0
+    sc = device.DeviceScene(flat)
+    images.append(sc.render(params)[0])
+    for img in images[1:]:
+        assert np.allclose(img, images[0], rtol=1e-4, atol=1e-5)  # float atomics: summation order only
+
+
 def test_async_job_boundary():
     """BlockRenderer-style boundary: start, poll done(), progressive reads, final result."""
     lib = capi.product()
