@@ -1056,6 +1056,8 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
     pass.sampleStride = p->sample_stride;
     pass.maxDepth = p->max_depth;
     pass.sw = p->screen_width, pass.sh = p->screen_height, pass.sd = p->screen_distance;
+    pass.twoOverWidth = 2.f / (float)p->width, pass.twoOverHeight = 2.f / (float)p->height;
+    pass.byPixels = FastDivisor::make((uint32_t)rw * (uint32_t)rh), pass.byRowWidth = FastDivisor::make((uint32_t)rw);
     pass.seed = p->seed;
     pass.flags = p->flags;
     uint64_t launches = 0;

@@ -84,6 +84,9 @@ enum
 #ifndef PTB_PLANE_SELECT
 #define PTB_PLANE_SELECT 0
 #endif
+#ifndef PTB_INPLACE_A1
+#define PTB_INPLACE_A1 1
+#endif
 #ifndef PTB_TAIL_CLOSED
 #define PTB_TAIL_CLOSED 1
 #endif
@@ -220,10 +223,16 @@ PTB_MERGE_FN int fastMerge(uint32_t poolBase, int cap, float *ovf, size_t ovfStr
         }
         return a0 + 1;
     }
-    if(b0 - a0 == 1 && top - b0 == 1)
-        return mergeListsT(pool, kind, a0, b0, top, a0); // both inputs are in registers before the first output
-    int end = mergeListsT(pool, kind, a0, b0, top, top);
-    int n = end - top;
+    // A single-span A is in a register before the first output is written, and of B only spans already
+    // read can be overwritten (output k is written after k spans were read, and A's slot comes first):
+    // such merges run in place.  (Difference may split A in two, so it needs a single-span B as well.)
+    // Otherwise the output is appended behind B and moved down.  One copy of the state machines either way.
+    const bool inPlace = b0 - a0 == 1 && (top - b0 == 1 || (PTB_INPLACE_A1 && (op == FA_UNION || op == FA_INTERSECTION)));
+    const int dst = inPlace ? a0 : top;
+    const int end = mergeListsT(pool, kind, a0, b0, top, dst);
+    if(inPlace)
+        return end;
+    const int n = end - top;
     for(int i = 0; i < n; i++)
         pool.store(a0 + i, pool.load(top + i));
     return a0 + n;

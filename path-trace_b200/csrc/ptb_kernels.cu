@@ -293,16 +293,17 @@ __device__ __forceinline__ void queueLoad(const RayQueue &q, unsigned idx, PathS
 __device__ __forceinline__ void cameraSample(const RenderPass &pass, unsigned nPix, unsigned long long i, PathState &ps)
 {
     const unsigned i32 = (unsigned)i; // the queue capacity check keeps pixels x samples per pass below 2^32
-    unsigned s = i32 / nPix, p = i32 - s * nPix;
-    int px = pass.x0 + (int)(p % (unsigned)pass.rw), py = pass.y0 + (int)(p / (unsigned)pass.rw);
+    unsigned s = pass.byPixels.div(i32), p = i32 - s * nPix;
+    unsigned row = pass.byRowWidth.div(p);
+    int px = pass.x0 + (int)(p - row * (unsigned)pass.rw), py = pass.y0 + (int)row;
     ps.pixel = (unsigned)py * (unsigned)pass.width + (unsigned)px;
     ps.sample = (unsigned)(pass.sampleBase + (int)s * pass.sampleStride);
     Philox rng;
     rngInit(rng, pass.seed, ps.pixel, ps.sample, 0u);
     uint4 u = rngNext4(rng);
     ps.rngBlock = rng.block;
-    float x = 2.f * ((float)px + u01(u.x)) / (float)pass.width - 1.f;
-    float y = 1.f - 2.f * ((float)py + u01(u.y)) / (float)pass.height;
+    float x = fmaf((float)px + u01(u.x), pass.twoOverWidth, -1.f);
+    float y = fmaf((float)py + u01(u.y), -pass.twoOverHeight, 1.f);
     ps.o = mk(0.f, 0.f, 0.f);
     ps.d = mk(x * pass.sw, y * pass.sh, -pass.sd);
     ps.thr = mk(1.f, 1.f, 1.f);
