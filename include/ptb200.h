@@ -242,6 +242,13 @@ int ptb200_render_accumulate_device(PtbScene *scene, const PtbRenderParams *para
 /* rgba[i] = (accum.rgb / accum.a, 1) where accum.a > 0, else 0.  In place allowed. */
 int ptb200_resolve_device(const void *d_accum4, void *d_rgba4, size_t n_pixels, void *stream);
 
+/* 8-bit display conversion of the reference's main loop (src/test.cpp:992-995):
+ * byte = max(0, min(255, (int)floor(256 * c / count))) per channel, in float, in that order; output
+ * is r,g,b,255 per pixel.  divide_by_alpha != 0: count = the pixel's alpha (an accumulation buffer;
+ * alpha 0 gives black); else count = 1 (a resolved image).  _device: both buffers on the device. */
+int ptb200_display8_device(const void *d_rgba4, void *d_rgbx8, size_t n_pixels, int divide_by_alpha, void *stream);
+int ptb200_display8(const float *rgba, size_t n_pixels, int divide_by_alpha, uint8_t *rgbx8);
+
 /* Progressive / asynchronous boundary mirroring BlockRenderer::done()/copyToBuffer()
  * (reference src/test.cpp:310-323).  One job at a time per scene. */
 typedef struct PtbJob PtbJob;

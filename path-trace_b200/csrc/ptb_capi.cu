@@ -1199,6 +1199,36 @@ extern "C" int ptb200_render(PtbScene *s, const PtbRenderParams *p, float *rgba_
     return PTB_OK;
 }
 
+extern "C" int ptb200_display8_device(const void *d_rgba4, void *d_rgbx8, size_t n_pixels, int divide_by_alpha, void *stream)
+{
+    if(!d_rgba4 || !d_rgbx8)
+        return fail(PTB_EINVAL, "null argument");
+    if(n_pixels == 0)
+        return PTB_OK;
+    launchDisplay8((const float4 *)d_rgba4, (uchar4 *)d_rgbx8, n_pixels, divide_by_alpha != 0, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return PTB_OK;
+}
+
+extern "C" int ptb200_display8(const float *rgba, size_t n_pixels, int divide_by_alpha, uint8_t *rgbx8)
+{
+    if(!rgba || !rgbx8)
+        return fail(PTB_EINVAL, "null argument");
+    if(n_pixels == 0)
+        return PTB_OK;
+    int nDev = 0;
+    if(cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0)
+        return fail(PTB_ENODEV, "no CUDA device: libptb200 has no CPU fallback");
+    DeviceBuffer in, out;
+    CU(in.ensure(n_pixels * 16));
+    CU(out.ensure(n_pixels * 4));
+    CU(cudaMemcpy(in.p, rgba, n_pixels * 16, cudaMemcpyHostToDevice));
+    launchDisplay8((const float4 *)in.p, (uchar4 *)out.p, n_pixels, divide_by_alpha != 0, nullptr);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(rgbx8, out.p, n_pixels * 4, cudaMemcpyDeviceToHost));
+    return PTB_OK;
+}
+
 // ---- asynchronous / progressive boundary (BlockRenderer::done / copyToBuffer) -----------------------
 static void jobMain(PtbJob *job)
 {

@@ -589,6 +589,41 @@ void launchResolve(const float4 *accum, float4 *rgba, size_t nPixels, cudaStream
     resolveKernel<<<blocks, 256, 0, stream>>>(accum, rgba, nPixels);
 }
 
+// ---- 8-bit display conversion (reference src/test.cpp:992-995) ------------------------------------
+// byte = max(0, min(255, (int)floor(256 * c / count))) per channel, float arithmetic in that order;
+// count = the pixel's finished samples (alpha of an accumulation buffer), or 1 for a resolved image.
+// 16 B read + 4 B written per pixel: HBM-bound, coalesced, one pixel per thread and trip.
+__global__ void display8Kernel(const float4 *__restrict__ rgba, uchar4 *__restrict__ out, size_t n, int divideByAlpha)
+{
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for(size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        float4 a = __ldcs(&rgba[i]);
+        float count = divideByAlpha ? a.w : 1.f;
+        uchar4 o = make_uchar4(0, 0, 0, 255);
+        if(count > 0.f)
+        {
+            float r = floorf(__fdiv_rn(__fmul_rn(256.f, a.x), count)), g = floorf(__fdiv_rn(__fmul_rn(256.f, a.y), count)),
+                  b = floorf(__fdiv_rn(__fmul_rn(256.f, a.z), count));
+            // (int) of a NaN or of a value outside the int range is INT_MIN on the x86-64 reference build
+            // (cvttss2si's "integer indefinite"), which the clamp then turns into 0
+            o.x = (unsigned char)((r >= 2147483648.f || r < -2147483648.f || r != r) ? 0 : max(0, min(255, (int)r)));
+            o.y = (unsigned char)((g >= 2147483648.f || g < -2147483648.f || g != g) ? 0 : max(0, min(255, (int)g)));
+            o.z = (unsigned char)((b >= 2147483648.f || b < -2147483648.f || b != b) ? 0 : max(0, min(255, (int)b)));
+        }
+        out[i] = o;
+    }
+}
+void launchDisplay8(const float4 *rgba, uchar4 *out, size_t nPixels, bool divideByAlpha, cudaStream_t stream)
+{
+    int blocks = (int)((nPixels + 255) / 256);
+    if(blocks > 148 * 8)
+        blocks = 148 * 8;
+    if(blocks < 1)
+        blocks = 1;
+    display8Kernel<<<blocks, 256, 0, stream>>>(rgba, out, nPixels, divideByAlpha ? 1 : 0);
+}
+
 // ---- inspection kernels (known-answer tests through the C ABI) ----------------------------------
 __global__ void textureEvalKernel(DevScene sc, int root, const float *__restrict__ pos, size_t n, float *__restrict__ rgb, float *__restrict__ f, uint32_t flags)
 {

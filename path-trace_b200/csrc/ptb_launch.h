@@ -86,6 +86,7 @@ void launchShade(const DevScene &sc, int blocks, bool primary, const RenderPass 
                  unsigned *outCount, cudaStream_t stream);
 int shadeBlocksPerSm(bool primary);
 void launchResolve(const float4 *accum, float4 *rgba, size_t nPixels, cudaStream_t stream);
+void launchDisplay8(const float4 *rgba, uchar4 *out, size_t nPixels, bool divideByAlpha, cudaStream_t stream);
 void launchTextureEval(const DevScene &sc, int root, const float *pos, size_t n, float *rgb, float *f, uint32_t flags, cudaStream_t stream);
 void launchScatterSample(const float *normal, const float *refl, float scatter, size_t n, uint64_t seed, uint32_t flags, float *dirs, cudaStream_t stream);
 // FMA-chain microbenchmark: returns lane-FMAs executed.

@@ -85,7 +85,7 @@ assert HIT_DTYPE.itemsize == 32 and SPAN_DTYPE.itemsize == 48
 # every symbol include/ptb200.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
     "ptb200_last_error", "ptb200_abi_version", "ptb200_device_count", "ptb200_trim", "ptb200_scene_create", "ptb200_scene_destroy", "ptb200_image_upload",
-    "ptb200_intersect", "ptb200_intersect_device", "ptb200_texture_eval", "ptb200_render", "ptb200_render_accumulate_device", "ptb200_resolve_device",
+    "ptb200_intersect", "ptb200_intersect_device", "ptb200_texture_eval", "ptb200_render", "ptb200_render_accumulate_device", "ptb200_resolve_device", "ptb200_display8_device", "ptb200_display8",
     "ptb200_render_async", "ptb200_job_done", "ptb200_job_read", "ptb200_job_wait", "ptb200_job_destroy", "ptb200_sample_scatter", "ptb200_fp32_peak",
 ]
 
@@ -180,6 +180,8 @@ def product():
         lib.ptb200_render.argtypes = [_vp, C.POINTER(PtbRenderParams), _vp, C.POINTER(PtbStats)]
         lib.ptb200_render_accumulate_device.argtypes = [_vp, C.POINTER(PtbRenderParams), _vp, C.POINTER(PtbStats), _vp]
         lib.ptb200_resolve_device.argtypes = [_vp, _vp, _sz, _vp]
+        lib.ptb200_display8_device.argtypes = [_vp, _vp, _sz, _i, _vp]
+        lib.ptb200_display8.argtypes = [_vp, _sz, _i, _vp]
         lib.ptb200_render_async.argtypes = [_vp, C.POINTER(PtbRenderParams), C.POINTER(_vp)]
         lib.ptb200_job_done.argtypes = [_vp]
         lib.ptb200_job_read.argtypes = [_vp, _vp, _i, _i]

@@ -163,6 +163,39 @@ def test_passes_do_not_change_the_estimate():
     assert np.allclose(a, c, rtol=1e-4, atol=1e-5)
 
 
+def test_display8_matches_the_reference_conversion():
+    """max(0, min(255, (int)floor(256 * c / count))), reference src/test.cpp:992-995 (x86-64: (int) of a
+    NaN or out-of-range float is INT_MIN, hence 0 after the clamp)."""
+    lib = capi.product()
+    rs = np.random.RandomState(3)
+    n = 100003
+    rgba = rs.uniform(-0.2, 1.4, (n, 4)).astype(np.float32)
+    rgba[:, 3] = rs.randint(0, 5, n)
+    rgba[:16, 0] = [0.0, 1.0, 255.0 / 256.0, np.nextafter(np.float32(1), np.float32(0)), 1e-8, -1e-8, np.inf, -np.inf, np.nan, 1e7, 8.4e6, 3e38, -3e38, 0.5, 0.25, 0.999]
+    rgba[:16, 3] = 1
+
+    def want(divide):
+        count = np.where(divide, rgba[:, 3:4], np.float32(1)).astype(np.float32)
+        with np.errstate(all="ignore"):
+            v = np.floor((np.float32(256) * rgba[:, :3]) / count)
+            ok = np.isfinite(v) & (v < 2147483648.0) & (v >= -2147483648.0)
+            out = np.where(ok, np.clip(np.where(ok, v, 0), 0, 255), 0).astype(np.uint8)
+        out[(count <= 0)[:, 0]] = 0
+        return out
+
+    for divide in (0, 1):
+        got = np.zeros((n, 4), np.uint8)
+        assert lib.ptb200_display8(rgba.ctypes.data, n, divide, got.ctypes.data) == 0
+        assert np.array_equal(got[:, :3], want(bool(divide)))
+        assert (got[:, 3] == 255).all()
+    torch = pytest.importorskip("torch")
+    d_in = torch.from_numpy(rgba).cuda()
+    d_out = torch.zeros((n, 4), dtype=torch.uint8, device="cuda")
+    assert lib.ptb200_display8_device(d_in.data_ptr(), d_out.data_ptr(), n, 1, None) == 0
+    torch.cuda.synchronize()
+    assert np.array_equal(d_out.cpu().numpy()[:, :3], want(True))
+
+
 def test_scratch_cache_survives_scene_lifetimes_and_trim():
     """Scratch blocks are cached across scenes (include/ptb200.h: ptb200_trim): a scene created after
     another one was destroyed renders the same image from recycled (dirty) blocks, and again after a trim."""
