@@ -209,6 +209,11 @@ void encodeChannel(std::ofstream &os, const unsigned char *quads, size_t w, size
 }
 } // namespace
 
+namespace PathTrace
+{
+std::shared_ptr<ptb200::Image_data> loadPng(const std::string &fileName); // ptb200_png.cpp
+}
+
 Image::Image(std::string fileName, std::string format)
 {
     if(format == "")
@@ -223,7 +228,7 @@ Image::Image(std::string fileName, std::string format)
     if(format == "hdr" || format == "pic")
         data = loadRadiance(fileName);
     else if(format == "png")
-        throw ImageLoadError("png decoding is not available in this build (libpng absent): convert " + fileName + " to .hdr or upload raw RGBA");
+        data = PathTrace::loadPng(fileName);
     else
         throw ImageLoadError("invalid format");
 }

@@ -126,3 +126,107 @@ def test_image_errors():
         b.image_load("/nonexistent/file.hdr")
     with pytest.raises(RuntimeError):
         b.image_load("/tmp/noextension")
+
+
+# ---- PNG ingestion (host/ptb200_png.cpp; reference src/png_decoder.cpp:40-121 + src/image.cpp:60-73) ----
+def _png_chunk(kind, body):
+    import struct
+    import zlib
+    return struct.pack(">I", len(body)) + kind + body + struct.pack(">I", zlib.crc32(kind + body) & 0xFFFFFFFF)
+
+
+def _png_filter(kind, row, prev, bpp):
+    out = bytearray(len(row))
+    for i in range(len(row)):
+        a = row[i - bpp] if i >= bpp else 0
+        b = prev[i]
+        c = prev[i - bpp] if i >= bpp else 0
+        if kind == 0:
+            pred = 0
+        elif kind == 1:
+            pred = a
+        elif kind == 2:
+            pred = b
+        elif kind == 3:
+            pred = (a + b) >> 1
+        else:
+            p = a + b - c
+            pa, pb, pc = abs(p - a), abs(p - b), abs(p - c)
+            pred = a if pa <= pb and pa <= pc else b if pb <= pc else c
+        out[i] = (row[i] - pred) & 0xFF
+    return bytes(out)
+
+
+def _png_file(w, h, depth, ctype, rows, palette=None, interlace=0, pieces=3):
+    """rows: unfiltered scanline bytes; every filter type is used in turn; IDAT split into `pieces`."""
+    import struct
+    import zlib
+    channels = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ctype]
+    bpp = max(1, channels * depth // 8)
+    raw, prev = b"", bytes(len(rows[0]))
+    for y, row in enumerate(rows):
+        raw += bytes([y % 5]) + _png_filter(y % 5, row, prev, bpp)
+        prev = row
+    z = zlib.compress(raw, 6)
+    step = max(1, (len(z) + pieces - 1) // pieces)
+    out = b"\x89PNG\r\n\x1a\n" + _png_chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, ctype, 0, 0, interlace))
+    out += _png_chunk(b"tEXt", b"Comment\0made by the test")
+    if palette is not None:
+        out += _png_chunk(b"PLTE", bytes(palette))
+    for k in range(0, len(z), step):
+        out += _png_chunk(b"IDAT", z[k:k + step])
+    return out + _png_chunk(b"IEND", b"")
+
+
+def test_png_ingestion_matches_libpng_transforms_of_the_reference(tmp_path):
+    b = product_builder()
+    rs = np.random.RandomState(5)
+    w, h = 37, 11
+
+    def load(data, name):
+        path = str(tmp_path / name)
+        open(path, "wb").write(data)
+        return b.image_pixels(b.image_load(path))
+
+    # 8-bit RGB: alpha is the 0 filler (png_set_filler(png_ptr, 0, PNG_FILLER_AFTER))
+    rgb = rs.randint(0, 256, (h, w, 3)).astype(np.uint8)
+    rgb[3] = rgb[2]  # rows where Up predicts exactly
+    got = load(_png_file(w, h, 8, 2, [rgb[y].tobytes() for y in range(h)]), "rgb8.png")
+    assert got.shape == (h, w, 4)
+    assert np.array_equal(got[..., :3], rgb.astype(np.float32) / np.float32(255.0)) and (got[..., 3] == 0).all()
+    # 8-bit RGBA
+    rgba = rs.randint(0, 256, (h, w, 4)).astype(np.uint8)
+    got = load(_png_file(w, h, 8, 6, [rgba[y].tobytes() for y in range(h)], pieces=1), "rgba8.png")
+    assert np.array_equal(got, rgba.astype(np.float32) / np.float32(255.0))
+    # 16-bit RGB(A): the high byte (png_set_strip_16)
+    deep = rs.randint(0, 65536, (h, w, 4)).astype(">u2")
+    got = load(_png_file(w, h, 16, 6, [deep[y].tobytes() for y in range(h)]), "rgba16.png")
+    assert np.array_equal(got, (deep >> 8).astype(np.float32) / np.float32(255.0))
+    # palette, 8 / 4 / 2 / 1 bits per index
+    for depth in (8, 4, 2, 1):
+        n = 1 << depth
+        palette = rs.randint(0, 256, (n, 3)).astype(np.uint8)
+        index = rs.randint(0, n, (h, w)).astype(np.uint8)
+        rows = []
+        for y in range(h):
+            bits = "".join(format(int(v), "0%db" % depth) for v in index[y])
+            bits += "0" * (-len(bits) % 8)
+            rows.append(bytes(int(bits[k:k + 8], 2) for k in range(0, len(bits), 8)))
+        got = load(_png_file(w, h, depth, 3, rows, palette=palette.reshape(-1).tolist()), "pal%d.png" % depth)
+        assert np.array_equal(got[..., :3], palette[index].astype(np.float32) / np.float32(255.0)) and (got[..., 3] == 0).all()
+    # what the reference cannot load either, or mangles: errors, not garbage
+    gray = [bytes(w) for _ in range(h)]
+    for data, name in ((_png_file(w, h, 8, 0, gray), "gray.png"), (_png_file(w, h, 8, 2, [rgb[y].tobytes() for y in range(h)], interlace=1), "adam7.png"),
+                       (b"\x89PNG\r\n\x1a\n" + b"\0" * 40, "junk.png")):
+        with pytest.raises(RuntimeError):
+            load(data, name)
+    good = bytearray(_png_file(w, h, 8, 2, [rgb[y].tobytes() for y in range(h)]))
+    good[len(good) // 2] ^= 0x40  # a flipped bit inside IDAT: CRC error
+    with pytest.raises(RuntimeError):
+        load(bytes(good), "crc.png")
+    # and a file of the reference's own kind (8-bit RGB written by a stock encoder), when PIL is here
+    PIL = pytest.importorskip("PIL.Image")
+    path = str(tmp_path / "pil.png")
+    PIL.fromarray(rgb, "RGB").save(path, optimize=True)
+    got = b.image_pixels(b.image_load(path))
+    assert np.array_equal(got[..., :3], rgb.astype(np.float32) / np.float32(255.0)) and (got[..., 3] == 0).all()
