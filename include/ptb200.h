@@ -242,6 +242,38 @@ int ptb200_render_accumulate_device(PtbScene *scene, const PtbRenderParams *para
 /* rgba[i] = (accum.rgb / accum.a, 1) where accum.a > 0, else 0.  In place allowed. */
 int ptb200_resolve_device(const void *d_accum4, void *d_rgba4, size_t n_pixels, void *stream);
 
+/* Adaptive rendering: the pixel-skipping quadtree of the reference's tile renderer,
+ * RenderBlock::renderSquare / interpolateSquare / colorCloseEnough (src/test.cpp:423-499), opt-in
+ * (it changes the image: skipped pixels are bilinear blends of traced ones).  The image is cut into
+ * block_size x block_size tiles whose corners are traced; a square whose four corners are pairwise
+ * within min_color_delta (relative, |a-b|^2 <= delta^2 |a|^2) and whose edge is <= max_sample_size is
+ * interpolated, otherwise its five edge/centre midpoints are traced and its four quarters follow.
+ * The decisions, the interpolation arithmetic and the final image are exactly those of the reference
+ * for the same traced values; the walk is level-synchronous over all tiles instead of depth-first per
+ * tile, and a lattice point shared by two tiles is traced once (the reference traces it per tile).
+ * Reference values at 1920x1080: block_size 32, max_sample_size 9, min_color_delta 0.003
+ * (src/test.cpp:38,50).  params->x0..y1 must name the whole image.  source_out (nullable,
+ * width*height bytes): 1 = traced pixel, 2 = interpolated pixel.  lattice_out (nullable): the traced
+ * lattice, rows x pitch x 4 floats with pitch = ceil(width/block_size)*block_size + 1 and rows likewise
+ * from height — mean radiance and alpha 1 at every traced point (those on and beyond the right and
+ * bottom image edge included, which the reference traces too), zeros elsewhere. */
+typedef struct PtbAdaptiveParams {
+    int32_t block_size;      /* blockSize: power of two                                            */
+    int32_t max_sample_size; /* maximumSampleSize: largest square edge that may be interpolated    */
+    float min_color_delta;   /* minimumColorDelta                                                   */
+    int32_t reserved;
+} PtbAdaptiveParams;
+typedef struct PtbAdaptiveStats {
+    uint64_t pixels_traced;        /* lattice points traced (incl. those beyond the right/bottom edge) */
+    uint64_t pixels_interpolated;  /* visible pixels filled by interpolateSquare                       */
+    uint64_t squares_interpolated;
+    int32_t levels;                /* quadtree levels decided                                          */
+    int32_t reserved;
+} PtbAdaptiveStats;
+int ptb200_render_adaptive(PtbScene *scene, const PtbRenderParams *params, const PtbAdaptiveParams *adaptive,
+                           float *rgba_out, uint8_t *source_out, float *lattice_out, PtbStats *stats,
+                           PtbAdaptiveStats *adaptive_stats);
+
 /* 8-bit display conversion of the reference's main loop (src/test.cpp:992-995):
  * byte = max(0, min(255, (int)floor(256 * c / count))) per channel, in float, in that order; output
  * is r,g,b,255 per pixel.  divide_by_alpha != 0: count = the pixel's alpha (an accumulation buffer;

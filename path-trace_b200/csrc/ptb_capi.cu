@@ -139,6 +139,7 @@ struct ImageSlot
 struct RenderScratch
 {
     DeviceBuffer queues, hits, counters, overflow, accum;
+    DeviceBuffer adaptive; // value + interp frames, request flags, square and pixel lists of ptb200_render_adaptive
     unsigned *hostCounters = nullptr; // pinned
     size_t hostCountersLen = 0;
     std::vector<cudaEvent_t> events;
@@ -1000,12 +1001,22 @@ static int checkParams(const PtbRenderParams *p, int &x0, int &y0, int &rw, int 
     return PTB_OK;
 }
 
+// Adaptive rendering traces explicit lists of lattice points instead of a rectangle.
+struct PixelListArg
+{
+    const uint32_t *list; // device: y << 16 | x
+    unsigned count;
+    int pitch;            // lattice points per row of the accumulation frame
+};
+
 // Caller holds scene->lock and has made scene->device current.
-static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbStats *stats, cudaStream_t stream)
+static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbStats *stats, cudaStream_t stream, const PixelListArg *points = nullptr)
 {
     int x0, y0, rw, rh;
     if(int rc = checkParams(p, x0, y0, rw, rh))
         return rc;
+    if(points)
+        x0 = y0 = 0, rw = (int)points->count, rh = 1;
     RenderScratch &sx = s->scratch;
     CsgConfig cfg;
     if(int rc = chooseConfig(s, 2, sx.overflow, cfg))
@@ -1051,7 +1062,8 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
         sx.events.push_back(e);
     }
     RenderPass pass;
-    pass.width = p->width, pass.height = p->height;
+    pass.width = points ? points->pitch : p->width, pass.height = p->height;
+    pass.pixelList = points ? points->list : nullptr;
     pass.x0 = x0, pass.y0 = y0, pass.rw = rw, pass.rh = rh;
     pass.sampleStride = p->sample_stride;
     pass.maxDepth = p->max_depth;
@@ -1196,6 +1208,125 @@ extern "C" int ptb200_render(PtbScene *s, const PtbRenderParams *p, float *rgba_
         stats->ms_resolve = ms;
         stats->launches += 1;
     }
+    return PTB_OK;
+}
+
+// Adaptive rendering: RenderBlock::renderSquare's quadtree (reference src/test.cpp:423-499) run
+// level by level for all tiles at once.  Level `size` decides every square of that size (interpolate
+// or subdivide), the lattice points the subdivided ones ask for are traced as ONE pixel-list render
+// through the same wavefront kernels, then the next level follows.
+extern "C" int ptb200_render_adaptive(PtbScene *s, const PtbRenderParams *p, const PtbAdaptiveParams *ap, float *rgba_out, uint8_t *source_out, float *lattice_out,
+                                      PtbStats *stats, PtbAdaptiveStats *astats)
+{
+    if(!s || !rgba_out || !ap)
+        return fail(PTB_EINVAL, "null argument");
+    int x0, y0, rw, rh;
+    if(int rc = checkParams(p, x0, y0, rw, rh))
+        return rc;
+    if(rw != p->width || rh != p->height)
+        return fail(PTB_EINVAL, "adaptive rendering takes the whole image, not a rectangle");
+    const int B = ap->block_size;
+    if(B < 2 || B > 1024 || (B & (B - 1)) != 0)
+        return fail(PTB_EINVAL, "block_size must be a power of two in [2, 1024] (getBlockSize, reference src/test.cpp:40-48)");
+    if(ap->max_sample_size < 0 || !(ap->min_color_delta >= 0.f))
+        return fail(PTB_EINVAL, "bad max_sample_size / min_color_delta");
+    const int W = p->width, H = p->height;
+    const int tilesX = (W + B - 1) / B, tilesY = (H + B - 1) / B;
+    const int pitch = tilesX * B + 1, rows = tilesY * B + 1;
+    if(pitch > 65535 || rows > 65535)
+        return fail(PTB_EINVAL, "image too large for adaptive rendering (16-bit lattice coordinates)");
+    std::lock_guard<std::mutex> g(s->lock);
+    if(s->asyncBusy)
+        return fail(PTB_EBUSY, "an asynchronous render is running on this scene");
+    CU(cudaSetDevice(s->device));
+    RenderScratch &sx = s->scratch;
+    const size_t nLattice = (size_t)pitch * rows, nPix = (size_t)W * H;
+    const size_t maxSquares = std::max<size_t>((size_t)tilesX * tilesY, (size_t)(tilesX * B / 2) * (size_t)(tilesY * B / 2));
+    // carve-up of the adaptive block (all 16-byte aligned)
+    auto align = [](size_t n) { return (n + 255) & ~(size_t)255; };
+    const size_t oValue = 0, oInterp = oValue + align(nLattice * 16), oReq = oInterp + align(nLattice * 16), oSqA = oReq + align(nLattice * 4),
+                 oSqB = oSqA + align(maxSquares * 4), oList = oSqB + align(maxSquares * 4), oCnt = oList + align(nLattice * 4), oOut = oCnt + 256,
+                 oSrc = oOut + align(nPix * 16), total = oSrc + align(nPix);
+    CU(sx.adaptive.ensure(total));
+    CU(sx.accum.ensure(nLattice * 16));
+    char *base = (char *)sx.adaptive.p;
+    float4 *accum = (float4 *)sx.accum.p, *value = (float4 *)(base + oValue), *interp = (float4 *)(base + oInterp), *out = (float4 *)(base + oOut);
+    unsigned *requested = (unsigned *)(base + oReq), *counters = (unsigned *)(base + oCnt);
+    uint32_t *squares[2] = {(uint32_t *)(base + oSqA), (uint32_t *)(base + oSqB)}, *list = (uint32_t *)(base + oList);
+    uint8_t *source = (uint8_t *)(base + oSrc);
+    CU(cudaMemsetAsync(accum, 0, nLattice * 16, nullptr));
+    CU(cudaMemsetAsync(base, 0, oSqA, nullptr)); // value, interp, request flags
+    // level 0: the corners of every tile (src/test.cpp:504), traced once for the tiles that share them
+    std::vector<uint32_t> host;
+    for(int j = 0; j <= tilesY; j++)
+        for(int i = 0; i <= tilesX; i++)
+            host.push_back(((uint32_t)(j * B) << 16) | (uint32_t)(i * B));
+    unsigned nList = (unsigned)host.size();
+    CU(cudaMemcpyAsync(list, host.data(), host.size() * 4, cudaMemcpyHostToDevice, nullptr));
+    CU(cudaStreamSynchronize(nullptr));
+    host.clear();
+    for(int j = 0; j < tilesY; j++)
+        for(int i = 0; i < tilesX; i++)
+            host.push_back(((uint32_t)(j * B) << 16) | (uint32_t)(i * B));
+    unsigned nSquares = (unsigned)host.size();
+    CU(cudaMemcpyAsync(squares[0], host.data(), host.size() * 4, cudaMemcpyHostToDevice, nullptr));
+    CU(cudaStreamSynchronize(nullptr));
+    PtbStats sum;
+    memset(&sum, 0, sizeof(sum));
+    PtbAdaptiveStats as;
+    memset(&as, 0, sizeof(as));
+    auto traceList = [&](unsigned n) -> int {
+        if(n == 0u)
+            return PTB_OK;
+        PixelListArg arg{list, n, pitch};
+        PtbStats st;
+        if(int rc = renderPasses(s, p, accum, &st, nullptr, &arg))
+            return rc;
+        launchAdaptiveResolveList(accum, value, list, n, pitch, nullptr);
+        CU(cudaGetLastError());
+        sum.paths += st.paths, sum.rays += st.rays, sum.launches += st.launches + 1, sum.queue_bytes += st.queue_bytes;
+        sum.ms_total += st.ms_total, sum.ms_primary += st.ms_primary, sum.ms_bounce += st.ms_bounce;
+        sum.rays_primary += st.rays_primary, sum.rays_bounce += st.rays_bounce;
+        sum.ms_trace_primary += st.ms_trace_primary, sum.ms_trace_bounce += st.ms_trace_bounce;
+        as.pixels_traced += n;
+        return PTB_OK;
+    };
+    if(int rc = traceList(nList))
+        return rc;
+    int cur = 0;
+    for(int size = B; size >= 2 && nSquares > 0u; size /= 2)
+    {
+        CU(cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned), nullptr));
+        AdaptiveLevel lv;
+        lv.width = W, lv.height = H, lv.pitch = pitch, lv.size = size, lv.maxSampleSize = ap->max_sample_size;
+        lv.delta2 = ap->min_color_delta * ap->min_color_delta;
+        lv.squares = squares[cur], lv.nSquares = nSquares;
+        lv.value = value, lv.interp = interp, lv.requested = requested;
+        lv.childSquares = squares[cur ^ 1], lv.pixelList = list, lv.counters = counters;
+        launchAdaptiveDecide(lv, nullptr);
+        CU(cudaGetLastError());
+        unsigned c[4] = {0u, 0u, 0u, 0u};
+        CU(cudaMemcpy(c, counters, sizeof(c), cudaMemcpyDeviceToHost));
+        sum.launches += 1;
+        as.levels += 1;
+        as.squares_interpolated += c[2];
+        as.pixels_interpolated += c[3];
+        nSquares = c[0], nList = c[1], cur ^= 1;
+        if(int rc = traceList(nList))
+            return rc;
+    }
+    launchAdaptiveAssemble(value, interp, pitch, W, H, out, source, nullptr);
+    CU(cudaGetLastError());
+    sum.launches += 1;
+    CU(cudaMemcpy(rgba_out, out, nPix * 16, cudaMemcpyDeviceToHost));
+    if(source_out)
+        CU(cudaMemcpy(source_out, source, nPix, cudaMemcpyDeviceToHost));
+    if(lattice_out)
+        CU(cudaMemcpy(lattice_out, value, nLattice * 16, cudaMemcpyDeviceToHost));
+    if(stats)
+        *stats = sum;
+    if(astats)
+        *astats = as;
     return PTB_OK;
 }
 

@@ -294,8 +294,17 @@ __device__ __forceinline__ void cameraSample(const RenderPass &pass, unsigned nP
 {
     const unsigned i32 = (unsigned)i; // the queue capacity check keeps pixels x samples per pass below 2^32
     unsigned s = pass.byPixels.div(i32), p = i32 - s * nPix;
-    unsigned row = pass.byRowWidth.div(p);
-    int px = pass.x0 + (int)(p - row * (unsigned)pass.rw), py = pass.y0 + (int)row;
+    int px, py;
+    if(pass.pixelList)
+    { // adaptive rendering: an explicit list of lattice points
+        const uint32_t packed = __ldg(pass.pixelList + p);
+        px = (int)(packed & 0xFFFFu), py = (int)(packed >> 16);
+    }
+    else
+    {
+        unsigned row = pass.byRowWidth.div(p);
+        px = pass.x0 + (int)(p - row * (unsigned)pass.rw), py = pass.y0 + (int)row;
+    }
     ps.pixel = (unsigned)py * (unsigned)pass.width + (unsigned)px;
     ps.sample = (unsigned)(pass.sampleBase + (int)s * pass.sampleStride);
     Philox rng;
@@ -622,6 +631,116 @@ void launchDisplay8(const float4 *rgba, uchar4 *out, size_t nPixels, bool divide
     if(blocks < 1)
         blocks = 1;
     display8Kernel<<<blocks, 256, 0, stream>>>(rgba, out, nPixels, divideByAlpha ? 1 : 0);
+}
+
+// ---- adaptive quadtree (reference src/test.cpp:423-499, RenderBlock::renderSquare) ---------------
+// The reference walks each 32x32 tile depth-first; the walk only ever reads TRACED lattice points
+// (an interpolated value is never a corner of a later square: interpolation writes the half-open
+// square [x, x+s) x [y, y+s), corners of other squares lie on its closed far edges or were traced
+// earlier), so one level of the tree can be decided for all tiles at once.  Arithmetic is the
+// reference's, un-fused: Color = Vector3D, dot(v, v) = (x*x + y*y) + z*z (include/vector3d.h:102-110).
+__device__ __forceinline__ float absSquaredRn(float x, float y, float z) { return __fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z)); }
+// colorCloseEnough (src/test.cpp:437-440): |a - b|^2 <= delta^2 * |a|^2
+__device__ __forceinline__ bool colorCloseEnough(float4 a, float4 b, float delta2)
+{
+    return absSquaredRn(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y), __fsub_rn(a.z, b.z)) <= __fmul_rn(delta2, absSquaredRn(a.x, a.y, a.z));
+}
+// a + f * (b - a) per channel (src/test.cpp:428-434)
+__device__ __forceinline__ float4 lerpRn(float4 a, float4 b, float f)
+{
+    return make_float4(__fadd_rn(a.x, __fmul_rn(f, __fsub_rn(b.x, a.x))), __fadd_rn(a.y, __fmul_rn(f, __fsub_rn(b.y, a.y))), __fadd_rn(a.z, __fmul_rn(f, __fsub_rn(b.z, a.z))), 2.f);
+}
+
+__global__ void adaptiveDecideKernel(AdaptiveLevel lv)
+{
+    const unsigned stride = gridDim.x * blockDim.x;
+    for(unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < lv.nSquares; i += stride)
+    {
+        const uint32_t packed = lv.squares[i];
+        const int x = (int)(packed & 0xFFFFu), y = (int)(packed >> 16), s = lv.size;
+        if(x > lv.width || y > lv.height) // src/test.cpp:468-471
+            continue;
+        const float4 tl = lv.value[(size_t)y * lv.pitch + x], tr = lv.value[(size_t)y * lv.pitch + x + s];
+        const float4 bl = lv.value[(size_t)(y + s) * lv.pitch + x], br = lv.value[(size_t)(y + s) * lv.pitch + x + s];
+        const float d2 = lv.delta2;
+        if(colorCloseEnough(tl, tr, d2) && colorCloseEnough(tl, bl, d2) && colorCloseEnough(tl, br, d2) && colorCloseEnough(tr, bl, d2) && colorCloseEnough(tr, br, d2) &&
+           colorCloseEnough(bl, br, d2) && s <= lv.maxSampleSize)
+        { // interpolateSquare, src/test.cpp:423-436
+            atomicAdd(&lv.counters[2], 1u);
+            const int visW = min(s, lv.width - x), visH = min(s, lv.height - y);
+            if(visW > 0 && visH > 0)
+                atomicAdd(&lv.counters[3], (unsigned)(visW * visH));
+            for(int yy = 0; yy < s && y + yy < lv.height; yy++)
+            {
+                const float fy = __fdiv_rn((float)yy, (float)s);
+                const float4 l = lerpRn(tl, bl, fy), r = lerpRn(tr, br, fy);
+                for(int xx = 0; xx < s && x + xx < lv.width; xx++)
+                    lv.interp[(size_t)(y + yy) * lv.pitch + x + xx] = lerpRn(l, r, __fdiv_rn((float)xx, (float)s));
+            }
+            continue;
+        }
+        // subdivide (src/test.cpp:486-498): five more lattice points, four squares of half the size
+        const int h = s / 2, cx = x + h, cy = y + h;
+        const int mx[5] = {cx, x, cx, x + s, cx}, my[5] = {y, cy, cy, cy, y + s};
+#pragma unroll
+        for(int k = 0; k < 5; k++)
+            if(atomicExch(&lv.requested[(size_t)my[k] * lv.pitch + mx[k]], 1u) == 0u)
+                lv.pixelList[atomicAdd(&lv.counters[1], 1u)] = ((uint32_t)my[k] << 16) | (uint32_t)mx[k];
+        if(h > 1)
+        { // squares of size 1 only re-state their traced top-left pixel (src/test.cpp:472-476)
+            const unsigned at = atomicAdd(&lv.counters[0], 4u);
+            lv.childSquares[at] = ((uint32_t)y << 16) | (uint32_t)x, lv.childSquares[at + 1] = ((uint32_t)y << 16) | (uint32_t)cx;
+            lv.childSquares[at + 2] = ((uint32_t)cy << 16) | (uint32_t)x, lv.childSquares[at + 3] = ((uint32_t)cy << 16) | (uint32_t)cx;
+        }
+    }
+}
+void launchAdaptiveDecide(const AdaptiveLevel &lv, cudaStream_t stream)
+{
+    if(lv.nSquares == 0u)
+        return;
+    int blocks = (int)((lv.nSquares + 127u) / 128u);
+    adaptiveDecideKernel<<<blocks > 148 * 16 ? 148 * 16 : blocks, 128, 0, stream>>>(lv);
+}
+
+__global__ void adaptiveResolveListKernel(const float4 *__restrict__ accum, float4 *__restrict__ value, const uint32_t *__restrict__ pixelList, unsigned n, int pitch)
+{
+    const unsigned stride = gridDim.x * blockDim.x;
+    for(unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        const uint32_t packed = pixelList[i];
+        const size_t at = (size_t)(packed >> 16) * pitch + (packed & 0xFFFFu);
+        const float4 a = accum[at];
+        const float inv = a.w > 0.f ? 1.f / a.w : 0.f;
+        value[at] = make_float4(a.x * inv, a.y * inv, a.z * inv, 1.f);
+    }
+}
+void launchAdaptiveResolveList(const float4 *accum, float4 *value, const uint32_t *pixelList, unsigned n, int pitch, cudaStream_t stream)
+{
+    if(n == 0u)
+        return;
+    int blocks = (int)((n + 255u) / 256u);
+    adaptiveResolveListKernel<<<blocks > 148 * 8 ? 148 * 8 : blocks, 256, 0, stream>>>(accum, value, pixelList, n, pitch);
+}
+
+__global__ void adaptiveAssembleKernel(const float4 *__restrict__ value, const float4 *__restrict__ interp, int pitch, int width, int height, float4 *__restrict__ rgba,
+                                       uint8_t *__restrict__ source)
+{
+    const size_t n = (size_t)width * height, stride = (size_t)gridDim.x * blockDim.x;
+    for(size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        const size_t y = i / (size_t)width, x = i - y * (size_t)width, at = y * pitch + x;
+        const float4 t = interp[at];
+        const float4 v = t.w == 2.f ? t : value[at];
+        rgba[i] = make_float4(v.x, v.y, v.z, v.w > 0.f ? 1.f : 0.f);
+        if(source)
+            source[i] = (uint8_t)v.w;
+    }
+}
+void launchAdaptiveAssemble(const float4 *value, const float4 *interp, int pitch, int width, int height, float4 *rgba, uint8_t *source, cudaStream_t stream)
+{
+    size_t n = (size_t)width * height;
+    int blocks = (int)((n + 255) / 256);
+    adaptiveAssembleKernel<<<blocks > 148 * 8 ? 148 * 8 : (blocks < 1 ? 1 : blocks), 256, 0, stream>>>(value, interp, pitch, width, height, rgba, source);
 }
 
 // ---- inspection kernels (known-answer tests through the C ABI) ----------------------------------

@@ -72,6 +72,9 @@ struct RenderPass
     FastDivisor byPixels, byRowWidth;  // rw * rh and rw
     uint64_t seed;
     uint32_t flags;
+    // adaptive rendering: when non-null, sample index p of a pass names lattice point pixelList[p]
+    // (y << 16 | x) instead of a pixel of the rectangle; rw = list length, rh = 1, width = frame pitch
+    const uint32_t *pixelList;
 };
 
 void launchIntersect(const DevScene &sc, const CsgConfig &cfg, const float4 *origins, const float4 *dirs, size_t n, PtbHit *hits, PtbSpan *spans, int maxSpans,
@@ -87,6 +90,29 @@ void launchShade(const DevScene &sc, int blocks, bool primary, const RenderPass 
 int shadeBlocksPerSm(bool primary);
 void launchResolve(const float4 *accum, float4 *rgba, size_t nPixels, cudaStream_t stream);
 void launchDisplay8(const float4 *rgba, uchar4 *out, size_t nPixels, bool divideByAlpha, cudaStream_t stream);
+
+// Adaptive quadtree of RenderBlock::renderSquare (reference src/test.cpp:423-499), level-synchronous.
+struct AdaptiveLevel
+{
+    int width, height;       // image
+    int pitch;               // frame pitch (lattice points per row, > width)
+    int size;                // edge of the squares of this level
+    int maxSampleSize;       // maximumSampleSize (src/test.cpp:50)
+    float delta2;            // minimumColorDelta * minimumColorDelta (float product, src/test.cpp:439)
+    const uint32_t *squares; // y << 16 | x of every square of this level
+    unsigned nSquares;
+    const float4 *value;     // traced lattice points: mean radiance, alpha 1
+    float4 *interp;          // interpolated pixels: colour, alpha 2
+    unsigned *requested;     // per lattice point: 1 once it has been put on a pixel list
+    uint32_t *childSquares;  // out: squares of the next level (size / 2)
+    uint32_t *pixelList;     // out: lattice points to trace before the next level
+    unsigned *counters;      // [0] = child squares, [1] = pixel list length, [2] = squares interpolated, [3] = pixels interpolated
+};
+void launchAdaptiveDecide(const AdaptiveLevel &lv, cudaStream_t stream);
+// value[p] = (accum[p].rgb / accum[p].a, 1) for every listed lattice point
+void launchAdaptiveResolveList(const float4 *accum, float4 *value, const uint32_t *pixelList, unsigned n, int pitch, cudaStream_t stream);
+// rgba (width x height) = interpolated pixel where there is one, else the traced one; source: 1 traced, 2 interpolated
+void launchAdaptiveAssemble(const float4 *value, const float4 *interp, int pitch, int width, int height, float4 *rgba, uint8_t *source, cudaStream_t stream);
 void launchTextureEval(const DevScene &sc, int root, const float *pos, size_t n, float *rgb, float *f, uint32_t flags, cudaStream_t stream);
 void launchScatterSample(const float *normal, const float *refl, float scatter, size_t n, uint64_t seed, uint32_t flags, float *dirs, cudaStream_t stream);
 // FMA-chain microbenchmark: returns lane-FMAs executed.

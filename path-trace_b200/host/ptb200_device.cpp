@@ -42,6 +42,24 @@ void renderFrame(const PathTrace::Object *world, const PtbRenderParams &params, 
     renderFrame(scene, params, rgba, stats);
 }
 
+PtbAdaptiveParams adaptiveDefaults(int width, int height)
+{
+    // getBlockSize(ScreenWidth / 8) and maximumSampleSize = ScreenHeight / (480 / 4), src/test.cpp:40-50
+    int count = width / 8, size = 1024;
+    while(size > count && size > 4)
+        size /= 2;
+    PtbAdaptiveParams a;
+    a.block_size = std::max(2, size / 4);
+    a.max_sample_size = height / (480 / 4);
+    a.min_color_delta = 0.003f; // minimumColorDelta, src/test.cpp:38
+    a.reserved = 0;
+    return a;
+}
+void renderFrameAdaptive(const DeviceScene &scene, const PtbRenderParams &params, const PtbAdaptiveParams &adaptive, float *rgba, PtbStats *stats, PtbAdaptiveStats *adaptiveStats)
+{
+    check(ptb200_render_adaptive(scene.handle(), &params, &adaptive, rgba, NULL, NULL, stats, adaptiveStats));
+}
+
 GpuBlockRenderer::GpuBlockRenderer(const DeviceScene &scene, int x, int y, int size, const PtbRenderParams &frame) : job(NULL)
 {
     PtbRenderParams p = frame;

@@ -40,6 +40,13 @@ PtbRenderParams defaultParams(int width, int height, int spp, int depth = 16);
 void renderFrame(const PathTrace::Object *world, const PtbRenderParams &params, float *rgba, PtbStats *stats = NULL);
 void renderFrame(const DeviceScene &scene, const PtbRenderParams &params, float *rgba, PtbStats *stats = NULL);
 
+// The reference's adaptive tile renderer (RenderBlock::renderSquare, src/test.cpp:423-499) for the
+// whole frame: pixels inside squares whose corners agree are interpolated instead of traced.
+// adaptiveDefaults() gives the reference's constants for a frame size (src/test.cpp:38-50).
+PtbAdaptiveParams adaptiveDefaults(int width, int height);
+void renderFrameAdaptive(const DeviceScene &scene, const PtbRenderParams &params, const PtbAdaptiveParams &adaptive, float *rgba, PtbStats *stats = NULL,
+                         PtbAdaptiveStats *adaptiveStats = NULL);
+
 // Drop-in for the reference's BlockRenderer (src/test.cpp:310-323): construction starts the
 // work asynchronously, done() polls, copyToBuffer() may be called repeatedly while it runs and
 // writes only pixels that already have a value.

@@ -76,6 +76,14 @@ class PtbStats(C.Structure):
         return {name: getattr(self, name) for name, _ in self._fields_}
 
 
+class PtbAdaptiveParams(C.Structure):
+    _fields_ = [("block_size", C.c_int32), ("max_sample_size", C.c_int32), ("min_color_delta", C.c_float), ("reserved", C.c_int32)]
+
+
+class PtbAdaptiveStats(C.Structure):
+    _fields_ = [("pixels_traced", C.c_uint64), ("pixels_interpolated", C.c_uint64), ("squares_interpolated", C.c_uint64), ("levels", C.c_int32), ("reserved", C.c_int32)]
+
+
 # numpy record layouts of PtbHit / PtbSpan (32 and 48 bytes)
 HIT_DTYPE = np.dtype([("t", "<f4"), ("normal", "<f4", 3), ("kind", "<i4"), ("prim", "<i4"), ("material", "<i4"), ("n_spans", "<i4")])
 SPAN_DTYPE = np.dtype([("start", "<f4"), ("end", "<f4"), ("start_normal", "<f4", 3), ("end_normal", "<f4", 3), ("start_prim", "<i4"), ("end_prim", "<i4"),
@@ -85,7 +93,7 @@ assert HIT_DTYPE.itemsize == 32 and SPAN_DTYPE.itemsize == 48
 # every symbol include/ptb200.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
     "ptb200_last_error", "ptb200_abi_version", "ptb200_device_count", "ptb200_trim", "ptb200_scene_create", "ptb200_scene_destroy", "ptb200_image_upload",
-    "ptb200_intersect", "ptb200_intersect_device", "ptb200_texture_eval", "ptb200_render", "ptb200_render_accumulate_device", "ptb200_resolve_device", "ptb200_display8_device", "ptb200_display8",
+    "ptb200_intersect", "ptb200_intersect_device", "ptb200_texture_eval", "ptb200_render", "ptb200_render_adaptive", "ptb200_render_accumulate_device", "ptb200_resolve_device", "ptb200_display8_device", "ptb200_display8",
     "ptb200_render_async", "ptb200_job_done", "ptb200_job_read", "ptb200_job_wait", "ptb200_job_destroy", "ptb200_sample_scatter", "ptb200_fp32_peak",
 ]
 
@@ -178,6 +186,7 @@ def product():
         lib.ptb200_intersect_device.argtypes = [_vp, _vp, _vp, _sz, _vp, _vp, _i, C.c_uint32, _vp]
         lib.ptb200_texture_eval.argtypes = [_vp, _i, _vp, _sz, _vp, _vp, C.c_uint32]
         lib.ptb200_render.argtypes = [_vp, C.POINTER(PtbRenderParams), _vp, C.POINTER(PtbStats)]
+        lib.ptb200_render_adaptive.argtypes = [_vp, C.POINTER(PtbRenderParams), C.POINTER(PtbAdaptiveParams), _vp, _vp, _vp, C.POINTER(PtbStats), C.POINTER(PtbAdaptiveStats)]
         lib.ptb200_render_accumulate_device.argtypes = [_vp, C.POINTER(PtbRenderParams), _vp, C.POINTER(PtbStats), _vp]
         lib.ptb200_resolve_device.argtypes = [_vp, _vp, _sz, _vp]
         lib.ptb200_display8_device.argtypes = [_vp, _vp, _sz, _i, _vp]

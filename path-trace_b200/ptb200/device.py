@@ -104,6 +104,22 @@ class DeviceScene:
         check(capi.product().ptb200_render(self.handle, C.byref(params), out.ctypes.data, C.byref(stats)))
         return out, stats
 
+    def render_adaptive(self, params, block_size=32, max_sample_size=None, min_color_delta=0.003):
+        """ptb200_render_adaptive: the reference's pixel-skipping quadtree (src/test.cpp:423-499).
+        Defaults are the reference's constants (src/test.cpp:38,50).  Returns image, source map
+        (1 traced, 2 interpolated), traced lattice, PtbStats, PtbAdaptiveStats."""
+        ap = capi.PtbAdaptiveParams()
+        ap.block_size = block_size
+        ap.max_sample_size = params.height // (480 // 4) if max_sample_size is None else max_sample_size
+        ap.min_color_delta = min_color_delta
+        out = np.zeros((params.height, params.width, 4), np.float32)
+        source = np.zeros((params.height, params.width), np.uint8)
+        bs = max(1, block_size)  # bad sizes are rejected by the library, not here
+        lattice = np.zeros((-(-params.height // bs) * bs + 1, -(-params.width // bs) * bs + 1, 4), np.float32)
+        stats, astats = PtbStats(), capi.PtbAdaptiveStats()
+        check(capi.product().ptb200_render_adaptive(self.handle, C.byref(params), C.byref(ap), out.ctypes.data, source.ctypes.data, lattice.ctypes.data, C.byref(stats), C.byref(astats)))
+        return out, source, lattice, stats, astats
+
     def render_accumulate(self, params, accum, stream=None, want_stats=True):
         """Adds this call's radiance sums into a device (H, W, 4) float32 torch tensor."""
         stats = PtbStats()
