@@ -160,6 +160,10 @@ def run_ours(args):
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner) go to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
@@ -305,7 +309,8 @@ def run_ours(args):
         "stage_ms": {"primary": st.ms_primary, "bounce": st.ms_bounce, "total": st.ms_total, "trace_primary": st.ms_trace_primary, "trace_bounce": st.ms_trace_bounce},
         "cpu_baseline": cpu,
     }
-    print(json.dumps(out))
+    sys.stdout.flush()
+    os.write(json_fd, (json.dumps(out) + "\n").encode())
     if world_size > 1:
         dist.destroy_process_group()
 

@@ -46,11 +46,35 @@ struct CachedBlock
 static std::mutex g_cacheLock;
 static std::vector<CachedBlock> g_cache;
 
+// Image arrays (cudaArray, RGBA32F) of destroyed scenes, reused by size: cudaMallocArray / cudaFreeArray
+// of the 82 MB environment map cost tens of milliseconds per scene.
+struct CachedArray
+{
+    cudaArray_t array;
+    int w, h, device;
+};
+static std::vector<CachedArray> g_arrayCache;
+// Pinned staging for host -> array uploads from pageable memory (two halves, used alternately).
+static std::mutex g_stagingLock;
+static char *g_staging = nullptr;
+static const size_t kStagingHalf = size_t(8) << 20;
+static cudaEvent_t g_stagingDone[2] = {nullptr, nullptr};
+
 static void cacheTrim(int device)
 { // device < 0: every device
     std::vector<CachedBlock> drop;
+    std::vector<CachedArray> dropArrays;
     {
         std::lock_guard<std::mutex> g(g_cacheLock);
+        for(size_t i = 0; i < g_arrayCache.size();)
+            if(device < 0 || g_arrayCache[i].device == device)
+            {
+                dropArrays.push_back(g_arrayCache[i]);
+                g_arrayCache[i] = g_arrayCache.back();
+                g_arrayCache.pop_back();
+            }
+            else
+                i++;
         for(size_t i = 0; i < g_cache.size();)
             if(device < 0 || g_cache[i].device == device)
             {
@@ -67,6 +91,11 @@ static void cacheTrim(int device)
     {
         cudaSetDevice(b.device);
         cudaFree(b.p);
+    }
+    for(const CachedArray &a : dropArrays)
+    {
+        cudaSetDevice(a.device);
+        cudaFreeArray(a.array);
     }
     cudaSetDevice(current);
 }
@@ -203,8 +232,47 @@ int createImage(const float *rgba, int w, int h, ImageSlot &slot)
     if(!rgba || w <= 0 || h <= 0)
         return fail(PTB_EINVAL, "image with no pixels");
     cudaChannelFormatDesc fmt = cudaCreateChannelDesc<float4>();
-    CU(cudaMallocArray(&slot.array, &fmt, (size_t)w, (size_t)h));
-    CU(cudaMemcpy2DToArray(slot.array, 0, 0, rgba, (size_t)w * 16, (size_t)w * 16, (size_t)h, cudaMemcpyHostToDevice));
+    int device = 0;
+    CU(cudaGetDevice(&device));
+    {
+        std::lock_guard<std::mutex> g(g_cacheLock);
+        for(size_t i = 0; i < g_arrayCache.size(); i++)
+            if(g_arrayCache[i].w == w && g_arrayCache[i].h == h && g_arrayCache[i].device == device)
+            {
+                slot.array = g_arrayCache[i].array;
+                g_arrayCache[i] = g_arrayCache.back();
+                g_arrayCache.pop_back();
+                break;
+            }
+    }
+    if(!slot.array)
+        CU(cudaMallocArray(&slot.array, &fmt, (size_t)w, (size_t)h));
+    slot.w = w, slot.h = h;
+    const size_t rowBytes = (size_t)w * 16;
+    if((size_t)h * rowBytes < (size_t(1) << 20) || rowBytes > kStagingHalf)
+        CU(cudaMemcpy2DToArray(slot.array, 0, 0, rgba, rowBytes, rowBytes, (size_t)h, cudaMemcpyHostToDevice));
+    else
+    { // the caller's buffer is pageable: copy it through pinned staging in 8 MB pieces, the CPU copy of
+      // piece k+1 overlapping the DMA of piece k (the driver's own pageable path ran at < 2 GB/s here)
+        std::lock_guard<std::mutex> g(g_stagingLock);
+        if(!g_staging)
+        {
+            CU(cudaMallocHost((void **)&g_staging, 2 * kStagingHalf));
+            CU(cudaEventCreateWithFlags(&g_stagingDone[0], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&g_stagingDone[1], cudaEventDisableTiming));
+        }
+        const int rowsPerPiece = (int)(kStagingHalf / rowBytes);
+        int k = 0;
+        for(int y = 0; y < h; y += rowsPerPiece, k ^= 1)
+        {
+            const int rows = std::min(rowsPerPiece, h - y);
+            CU(cudaEventSynchronize(g_stagingDone[k])); // the copy that last used this half has finished
+            memcpy(g_staging + k * kStagingHalf, (const char *)rgba + (size_t)y * rowBytes, (size_t)rows * rowBytes);
+            CU(cudaMemcpy2DToArrayAsync(slot.array, 0, (size_t)y, g_staging + k * kStagingHalf, rowBytes, rowBytes, (size_t)rows, cudaMemcpyHostToDevice, nullptr));
+            CU(cudaEventRecord(g_stagingDone[k], nullptr));
+        }
+        CU(cudaStreamSynchronize(nullptr));
+    }
     cudaResourceDesc res;
     memset(&res, 0, sizeof(res));
     res.resType = cudaResourceTypeArray;
@@ -715,7 +783,28 @@ static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s)
             mats[i].tex[k] = d->materials[i].tex[k];
         mats[i].ior = d->materials[i].ior;
         mats[i].iorIn = (float)(1.0 / d->materials[i].ior); // `ior = 1.0 / material->ior`, path-trace.h:79
-        mats[i].pad = 0;
+        mats[i].constMask = 0;
+        mats[i].emissive = mats[i].reflect = mats[i].transmit = make_float4(0.f, 0.f, 0.f, 0.f);
+        mats[i].scatterF = mats[i].trcF = mats[i].pad0 = mats[i].pad1 = 0.f;
+        for(int k = 0; k < 5; k++)
+        {
+            const PtbTexOp &op = d->texops[d->materials[i].tex[k]];
+            if(op.kind != PTB_TEX_CONST)
+                continue;
+            const float *c = d->texdata + op.arg;
+            const float4 v = make_float4(c[0], c[1], c[2], (c[0] + c[1] + c[2]) * (1.0f / 3.0f)); // meanRgb, ptb_texture.cuh
+            mats[i].constMask |= 1 << k;
+            if(k == PTB_MAT_EMISSIVE)
+                mats[i].emissive = v;
+            else if(k == PTB_MAT_REFLECT)
+                mats[i].reflect = v;
+            else if(k == PTB_MAT_TRANSMIT)
+                mats[i].transmit = v;
+            else if(k == PTB_MAT_SCATTER)
+                mats[i].scatterF = v.w;
+            else
+                mats[i].trcF = v.w;
+        }
     }
     std::vector<int2> texops(d->n_texops);
     for(int i = 0; i < d->n_texops; i++)
@@ -755,7 +844,25 @@ extern "C" void ptb200_scene_destroy(PtbScene *s)
         if(im.linear)
             cudaDestroyTextureObject(im.linear);
         if(im.array)
-            cudaFreeArray(im.array);
+        {
+            cudaArray_t evict = nullptr;
+            int evictDevice = s->device;
+            {
+                std::lock_guard<std::mutex> g(g_cacheLock);
+                if(g_arrayCache.size() >= 32)
+                { // bounded: the oldest entry goes back to the driver
+                    evict = g_arrayCache.front().array, evictDevice = g_arrayCache.front().device;
+                    g_arrayCache.erase(g_arrayCache.begin());
+                }
+                g_arrayCache.push_back(CachedArray{im.array, im.w, im.h, s->device});
+            }
+            if(evict)
+            {
+                cudaSetDevice(evictDevice);
+                cudaFreeArray(evict);
+                cudaSetDevice(s->device);
+            }
+        }
     }
     for(void *p : s->allocs)
         cudaFree(p);
@@ -1024,9 +1131,15 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
     const size_t nPix = (size_t)rw * rh;
     int perPass = p->samples_per_pass;
     if(perPass <= 0)
-    { // 64 Mi paths in flight (8 samples per pixel at 3840x2160: measured +11 % over one sample per pass,
-      // the 34 launches and their tails are amortised), but never more than a quarter of the free HBM
-        size_t want = (size_t(64) << 20), freeB = 0, totalB = 0;
+    { // PTB_PATHS_IN_FLIGHT (default 128 Mi: 16 samples per pixel at 3840x2160; measured +11 % from 1 to 8
+      // samples per pass and +2 % from 8 to 16 — the 34 launches of a pass, half of them on nearly empty
+      // queues, are amortised), but never more than a quarter of the free HBM
+        static const size_t inFlight = [] {
+            const char *e = getenv("PTB_PATHS_IN_FLIGHT");
+            long long v = e ? atoll(e) : 0;
+            return v > 0 ? (size_t)v : (size_t(128) << 20);
+        }();
+        size_t want = inFlight, freeB = 0, totalB = 0;
         if(cudaMemGetInfo(&freeB, &totalB) == cudaSuccess && sx.queues.bytes == 0)
             want = std::min(want, std::max<size_t>(size_t(1) << 20, freeB / 4 / 136));
         perPass = (int)std::max<size_t>(1, want / nPix);

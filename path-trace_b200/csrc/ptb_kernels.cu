@@ -307,10 +307,8 @@ __device__ __forceinline__ void cameraSample(const RenderPass &pass, unsigned nP
     }
     ps.pixel = (unsigned)py * (unsigned)pass.width + (unsigned)px;
     ps.sample = (unsigned)(pass.sampleBase + (int)s * pass.sampleStride);
-    Philox rng;
-    rngInit(rng, pass.seed, ps.pixel, ps.sample, 0u);
-    uint4 u = rngNext4(rng);
-    ps.rngBlock = rng.block;
+    const uint2 u = cameraJitter(pass.seed, ps.pixel, ps.sample);
+    ps.rngBlock = 0u;
     float x = fmaf((float)px + u01(u.x), pass.twoOverWidth, -1.f);
     float y = fmaf((float)py + u01(u.y), -pass.twoOverHeight, 1.f);
     ps.o = mk(0.f, 0.f, 0.f);

@@ -113,6 +113,22 @@ __device__ __forceinline__ void rngInit(Philox &r, uint64_t seed, uint32_t pixel
     r.block = block;
     r.have = 0;
 }
+// Sub-pixel jitter of a camera sample: two 32-bit words from an integer hash of (seed, pixel, sample)
+// (the 'lowbias32' finaliser twice).  The primary trace kernel and the primary shade kernel both
+// regenerate the camera ray, so this runs twice per path; a Philox block here was 80 of the ~1100
+// instructions of a camera ray.  Shading keeps Philox (blocks 0, 1, ... of the same stream).
+__device__ __forceinline__ uint32_t mix32(uint32_t h)
+{
+    h ^= h >> 16, h *= 0x7FEB352Du;
+    h ^= h >> 15, h *= 0x846CA68Bu;
+    return h ^ (h >> 16);
+}
+__device__ __forceinline__ uint2 cameraJitter(uint64_t seed, uint32_t pixel, uint32_t sample)
+{
+    const uint32_t a = mix32(pixel ^ (uint32_t)seed) + sample * 0x9E3779B1u;
+    const uint32_t x = mix32(a ^ (uint32_t)(seed >> 32));
+    return make_uint2(x, mix32(x + 0x85EBCA77u + a));
+}
 __device__ __forceinline__ uint4 rngNext4(Philox &r) { return philox4x32_10(r.c0, r.c1, r.block++, 0u, r.key0, r.key1); }
 // u32 -> closed [0,1]: float(u) / 2^32, the mapping of the reference's
 // uniform_real_distribution<float>(0,1) over a 32-bit engine (include/vector3d.h:26-33).

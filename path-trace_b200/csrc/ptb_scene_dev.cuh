@@ -18,7 +18,10 @@ struct DevMaterial
     int tex[5];  // PTB_MAT_* texture roots
     float ior;   // relative ior when leaving the material (include/path-trace.h:93)
     float iorIn; // float(1.0 / ior): relative ior when entering (include/path-trace.h:79)
-    int pad;
+    int constMask; // bit k: texture k is a bare ColorTexture whose value is folded into the fields below
+    // folded constants (rgb, getFloat = mean rgb): one 16-byte load instead of texops -> texdata chains
+    float4 emissive, reflect, transmit;
+    float scatterF, trcF, pad0, pad1;
 };
 
 struct DevScene

@@ -138,12 +138,13 @@ __device__ __forceinline__ bool shadeVertex(const DevScene &sc, PathState &ps, c
     const bool bilinear = flags & PTB_FLAG_BILINEAR;
     const DevMaterial &m = sc.materials[hit.mat];
     V3 hitPos = Ar<false>::point(ps.o, ps.d, hit.t);
-    V3 e = texColor(sc, m.tex[PTB_MAT_EMISSIVE], hitPos, bilinear);
+    const int cm = m.constMask; // bare ColorTextures were folded into the material record at scene create
+    V3 e = (cm & (1 << PTB_MAT_EMISSIVE)) ? mk(m.emissive.x, m.emissive.y, m.emissive.z) : texColor(sc, m.tex[PTB_MAT_EMISSIVE], hitPos, bilinear);
     radiance.x += ps.thr.x * e.x, radiance.y += ps.thr.y * e.y, radiance.z += ps.thr.z * e.z;
     if(ps.depth == 0u || ps.strength < PTB_EPS) // path-trace.h:105-108
         return false;
     float addFactor = 1.f;
-    float trc = texFloat(sc, m.tex[PTB_MAT_TRC], hitPos, bilinear);
+    float trc = (cm & (1 << PTB_MAT_TRC)) ? m.trcF : texFloat(sc, m.tex[PTB_MAT_TRC], hitPos, bilinear);
     trc = fmaxf(0.f, fminf(1.f, trc));
     float refractFactor = trc > 0.f ? trc * refractStrength(ps.d, hit.ior, hit.n) : 0.f;
     if(refractFactor > PTB_EPS) // path-trace.h:111-121
@@ -164,7 +165,7 @@ __device__ __forceinline__ bool shadeVertex(const DevScene &sc, PathState &ps, c
             }
             if(take)
             {
-                V3 tr = texColor(sc, m.tex[PTB_MAT_TRANSMIT], hitPos, bilinear);
+                V3 tr = (cm & (1 << PTB_MAT_TRANSMIT)) ? mk(m.transmit.x, m.transmit.y, m.transmit.z) : texColor(sc, m.tex[PTB_MAT_TRANSMIT], hitPos, bilinear);
                 ps.strength = ps.strength * refractFactor * addFactor * Ar<false>::length(tr);
                 ps.thr = mk(ps.thr.x * tr.x * w, ps.thr.y * tr.y * w, ps.thr.z * tr.z * w);
                 ps.o = hitPos, ps.d = rd;
@@ -177,12 +178,12 @@ __device__ __forceinline__ bool shadeVertex(const DevScene &sc, PathState &ps, c
     if(addFactor < PTB_EPS)
         return false;
     // diffuse / specular reflection, path-trace.h:127-163
-    float scat = texFloat(sc, m.tex[PTB_MAT_SCATTER], hitPos, bilinear);
+    float scat = (cm & (1 << PTB_MAT_SCATTER)) ? m.scatterF : texFloat(sc, m.tex[PTB_MAT_SCATTER], hitPos, bilinear);
     scat = fmaxf(0.f, fminf(1.f, scat));
     int count = (int)(10000.f * ps.strength * addFactor * scat);
     if(scat <= PTB_EPS || count == 0)
         count = 1;
-    V3 refl = texColor(sc, m.tex[PTB_MAT_REFLECT], hitPos, bilinear);
+    V3 refl = (cm & (1 << PTB_MAT_REFLECT)) ? mk(m.reflect.x, m.reflect.y, m.reflect.z) : texColor(sc, m.tex[PTB_MAT_REFLECT], hitPos, bilinear);
     if(isZero(refl)) // zero-weight child: contributes exactly 0, not traced
         return false;
     V3 nd = vreflect(ps.d, hit.n);
