@@ -219,6 +219,7 @@ def run_ours(args):
     barrier()
     st = step(True)
     barrier()
+    spec_ready, spec_compile_ms, spec_passes, spec_total = scene.specialized()  # did the scene-specialised trace kernels run?
     counts = torch.tensor([st.rays, st.paths, st.launches, st.queue_bytes], dtype=torch.float64, device="cuda")
     if world_size > 1:
         dist.all_reduce(counts, op=dist.ReduceOp.SUM)
@@ -301,11 +302,13 @@ def run_ours(args):
         "gpu_launches": int(launches / world_size) * args.steps + args.steps * (1 if rank == 0 else 0),
         "clocks": sampler.summary(),
         "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic,
-                     "kernel": "tracePrimaryKernel (rank 0): %d launches, %.3f ms average, %.0f Mrays/s" % (n_trace_launches, trace_ms / n_trace_launches, st.rays_primary / (trace_ms * 1e-3) / 1e6 if trace_ms > 0 else 0.0),
+                     "kernel": ("ptbSpecTracePrimary (scene-specialised, NVRTC)" if spec_passes == spec_total and spec_total else "tracePrimaryKernel") + " (rank 0): %d launches, %.3f ms average, %.0f Mrays/s" % (n_trace_launches, trace_ms / n_trace_launches, st.rays_primary / (trace_ms * 1e-3) / 1e6 if trace_ms > 0 else 0.0),
                      "flops_per_ray_model": fpr, "whole_wavefront": {"achieved": st.rays * fpr / (stage_ms * 1e-3) / 1e12 if stage_ms > 0 else 0.0, "stage_ms": stage_ms},
                      "peak_source": "ptb200_fp32_peak FMA-chain microbenchmark on this GPU (MEASURED_PEAKS.json has no FP32 entry); %.2f T lane-FMA/s = 128 lanes x %d SMs x %.0f MHz" % (fma_per_s / 1e12, torch.cuda.get_device_properties(0).multi_processor_count, implied_mhz),
                      "hbm_queues": {"bound": "hbm", "achieved": queue_bytes / world_size / (stage_ms * 1e-3) / 1e9 if stage_ms > 0 else 0.0, "peak": hbm_peak, "unit": "GB/s",
                                     "frac": queue_bytes / world_size / (stage_ms * 1e-3) / 1e9 / hbm_peak if stage_ms > 0 else None, "bytes_per_ray": "16 B hit record + 176 B per queued ray (64 written, 64 + 32 read, 16 hit)"}},
+        "trace_kernels": {"specialized_passes": spec_passes, "passes": spec_total, "nvrtc_compile_ms": spec_compile_ms if spec_ready else None,
+                          "policy": os.environ.get("PTB_SPECIALIZE", "auto: programs <= 96 words, compiled in the background during warm-up")},
         "stage_ms": {"primary": st.ms_primary, "bounce": st.ms_bounce, "total": st.ms_total, "trace_primary": st.ms_trace_primary, "trace_bounce": st.ms_trace_bounce},
         "cpu_baseline": cpu,
     }

@@ -17,8 +17,17 @@
 #ifndef PTB200_H_INCLUDED
 #define PTB200_H_INCLUDED
 
+#ifdef __CUDACC_RTC__ /* compiled at run time by NVRTC (scene-specialised kernels): no system headers there */
+typedef unsigned char uint8_t;
+typedef unsigned short uint16_t;
+typedef int int32_t;
+typedef unsigned int uint32_t;
+typedef long long int64_t;
+typedef unsigned long long uint64_t;
+#else
 #include <stddef.h>
 #include <stdint.h>
+#endif
 
 #ifdef __cplusplus
 extern "C" {
@@ -163,9 +172,12 @@ enum {
                                nearest texel                                        */
     PTB_FLAG_REJECTION = 4u,/* scatter by the reference's literal rejection loops
                                (path-trace.h:142-158) instead of the divergence-free cap sampler   */
-    PTB_FLAG_ORIGIN0 = 8u   /* ptb200_intersect*: the caller promises every origin is (0,0,0), as for
+    PTB_FLAG_ORIGIN0 = 8u,  /* ptb200_intersect*: the caller promises every origin is (0,0,0), as for
                                all camera rays (path-trace.h:196); selects the camera-ray variant of
                                the fast evaluator, which the renderer's primary stage runs          */
+    PTB_FLAG_SPECIALIZE = 16u, /* run the scene-specialised trace kernels (below), compiling them now if
+                               need be; an error if that is not possible                              */
+    PTB_FLAG_INTERPRET = 32u   /* never run the scene-specialised kernels in this call                */
 };
 
 /* ---- rendering ------------------------------------------------------------------------------ */
@@ -200,6 +212,7 @@ typedef struct PtbStats {
 
 /* ---- entry points --------------------------------------------------------------------------- */
 
+#ifndef __CUDACC_RTC__ /* host entry points: not seen by the run-time compiled device code */
 const char *ptb200_last_error(void);
 int ptb200_abi_version(void);
 int ptb200_device_count(void);
@@ -270,9 +283,11 @@ typedef struct PtbAdaptiveStats {
     int32_t levels;                /* quadtree levels decided                                          */
     int32_t reserved;
 } PtbAdaptiveStats;
+#ifndef __CUDACC_RTC__
 int ptb200_render_adaptive(PtbScene *scene, const PtbRenderParams *params, const PtbAdaptiveParams *adaptive,
                            float *rgba_out, uint8_t *source_out, float *lattice_out, PtbStats *stats,
                            PtbAdaptiveStats *adaptive_stats);
+#endif
 
 /* 8-bit display conversion of the reference's main loop (src/test.cpp:992-995):
  * byte = max(0, min(255, (int)floor(256 * c / count))) per channel, in float, in that order; output
@@ -292,6 +307,23 @@ int ptb200_job_read(PtbJob *job, float *rgba, int width, int height);
 int ptb200_job_wait(PtbJob *job, PtbStats *stats);
 void ptb200_job_destroy(PtbJob *job);
 
+/* Scene-specialised trace kernels.  The CSG program of a scene is also printed as straight-line CUDA
+ * (every header, matrix and plane a literal) and compiled for sm_100a at run time with NVRTC; the trace
+ * kernels built from it compute exactly what the interpreting ones do with about half the instructions.
+ * By default a render / ray batch with >= 2^26 rays to trace starts that compile on a background thread
+ * and switches over when it is done (between passes, if need be); compiled kernels are kept per process
+ * and per distinct scene program.  Environment: PTB_SPECIALIZE=0 never, =1 compile and wait at first
+ * use.  Flags: PTB_FLAG_SPECIALIZE / PTB_FLAG_INTERPRET per call.  No reference counterpart (the
+ * reference walks a tree of virtual SpanIterators, include/object.h:10-24).
+ * _probe needs no GPU: validates desc, writes the generated source (NUL-terminated, truncated to
+ * source_capacity; *source_length = full length) and, when cubin_bytes != NULL, compiles it and reports
+ * the size of the sm_100a cubin.
+ * _specialized: 1 when the scene's specialised kernels are compiled and loaded, else 0; also reports how
+ * many wavefront passes of the last render call that asked for stats ran them. */
+int ptb200_specialize_probe(const PtbSceneDesc *desc, int which /* 0: render trace kernels, 1: ray-batch kernels */, char *source, size_t source_capacity,
+                            size_t *source_length, size_t *cubin_bytes);
+int ptb200_scene_specialized(PtbScene *scene, double *compile_ms, int *passes_specialized, int *passes_total);
+
 /* Draws n scatter directions (n x 3 floats, host) from the lobe sampler of the shading kernel for
  * one unit normal, un-normalised mirror vector and scatter coefficient (reference
  * include/path-trace.h:140-158); (0,0,0) marks a dropped vertex.  For statistical checks. */
@@ -300,6 +332,7 @@ int ptb200_sample_scatter(const float *normal, const float *mirror, float scatte
 /* FP32 FMA-chain microbenchmark on the current device: measured lane-FMA/s (the FP32 issue-peak
  * denominator of the roofline). */
 int ptb200_fp32_peak(double *fma_per_second, double *sm_clock_mhz);
+#endif /* !__CUDACC_RTC__ */
 
 #ifdef __cplusplus
 }

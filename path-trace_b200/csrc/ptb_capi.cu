@@ -14,6 +14,7 @@
 
 #include "ptb_launch.h"
 #include "ptb_csg_fast.cuh"
+#include "ptb_specialize.h"
 
 using namespace ptb;
 
@@ -195,6 +196,14 @@ struct PtbScene
     std::mutex lock; // one render / intersect call at a time per scene
     RenderScratch scratch;
     bool asyncBusy = false;
+    // scene-specialised trace kernels (ptb_specialize.cu): compiled on first use by a render or ray batch
+    // large enough to pay for the compile, or at once with PTB_FLAG_SPECIALIZE
+    std::vector<uint4> fastHost;
+    std::string specSource[2]; // SPEC_TRACE, SPEC_INTERSECT
+    int lastSpecPasses = 0, lastPasses = 0; // of the last render call with stats
+    const SpecKernels *spec = nullptr;
+    bool specTried = false;
+    DeviceBuffer specOverflow;
 };
 
 struct PtbJob
@@ -654,7 +663,7 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
     }
 }
 
-static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s)
+static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> *fastOnly = nullptr)
 {
     if(!d || d->abi_version != PTB200_ABI_VERSION)
         return fail(PTB_EINVAL, "scene description has a different abi_version");
@@ -662,14 +671,17 @@ static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s)
         return fail(PTB_EINVAL, "empty scene");
     if(d->n_prims > 32767)
         return fail(PTB_EINVAL, "more than 32767 primitives (boundary tags are 16 bits)");
-    int nDev = 0;
-    if(cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0)
-        return fail(PTB_ENODEV, "no CUDA device: libptb200 has no CPU fallback");
-    CU(cudaGetDevice(&s->device));
-    cudaDeviceProp prop;
-    CU(cudaGetDeviceProperties(&prop, s->device));
-    s->smCount = prop.multiProcessorCount;
-    s->smemOptin = prop.sharedMemPerBlockOptin;
+    if(!fastOnly)
+    {
+        int nDev = 0;
+        if(cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0)
+            return fail(PTB_ENODEV, "no CUDA device: libptb200 has no CPU fallback");
+        CU(cudaGetDevice(&s->device));
+        cudaDeviceProp prop;
+        CU(cudaGetDeviceProperties(&prop, s->device));
+        s->smCount = prop.multiProcessorCount;
+        s->smemOptin = prop.sharedMemPerBlockOptin;
+    }
 
     // validate tables
     for(int i = 0; i < d->n_chains; i++)
@@ -759,6 +771,12 @@ static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s)
         return fail(PTB_EINVAL, "CSG tree needs more than 32 pending operands (right-deep nesting); rebalance it");
     if(poolBound > 65535)
         return fail(PTB_EINVAL, "scene too large for 16-bit span-pool offsets");
+    if(fastOnly)
+    { // ptb200_specialize_probe: validation and the compiled stream only, no device
+        *fastOnly = fast;
+        return PTB_OK;
+    }
+    s->fastHost = fast;
     prog.push_back(make_uint4(DK_END, 0, 0, 0));
 
     std::vector<float4> geo(d->n_prims);
@@ -954,6 +972,85 @@ static int chooseConfig(PtbScene *s, int which, DeviceBuffer &overflow, CsgConfi
     return PTB_OK;
 }
 
+// ---- scene-specialised kernels: when to use them, and how they are launched -------------------------
+// PTB_SPECIALIZE=0 never (unless PTB_FLAG_SPECIALIZE), =1 compile at first use and wait, default: a call
+// with at least 2^26 rays to trace starts the compile in the background and keeps interpreting until
+// the kernels are there (they give the same results, so a frame may switch between passes).
+struct SpecConfig
+{
+    const SpecKernels *k = nullptr;
+    CsgConfig cfg;
+};
+static int specMode()
+{
+    static const int mode = [] {
+        const char *e = getenv("PTB_SPECIALIZE");
+        return e ? atoi(e) : -1;
+    }();
+    return mode;
+}
+// work = rays this call is going to trace.  Leaves sp.k NULL when the call should interpret.
+static int chooseSpec(PtbScene *s, uint32_t flags, double work, int which, SpecConfig &sp)
+{
+    sp.k = nullptr;
+    const bool force = (flags & PTB_FLAG_SPECIALIZE) != 0;
+    // Straight-line code is ~35 instructions (560 bytes) per leaf where the interpreter reads 64 bytes of
+    // program: beyond a few dozen leaves the kernels stop fitting the SM's instruction cache and instruction
+    // fetch becomes the bound (ncu, C4's 70 leaves: 39 % fewer instructions executed, but 15-36 stall
+    // cycles per issue waiting for instructions — profiles/r01m_spec_*.txt), so only small programs are
+    // specialised unless the caller insists.
+    static const size_t maxWords = [] {
+        const char *e = getenv("PTB_SPEC_MAX_WORDS");
+        return e && atoi(e) > 0 ? (size_t)atoi(e) : (size_t)96;
+    }();
+    if((flags & (PTB_FLAG_INTERPRET | PTB_FLAG_EXACT)) || (!force && (specMode() == 0 || s->fastHost.size() > maxWords)) || s->fastHost.size() > 4096)
+    {
+        if(force)
+            return fail(PTB_EINVAL, "PTB_FLAG_SPECIALIZE cannot be combined with PTB_FLAG_INTERPRET / PTB_FLAG_EXACT, and needs a program of at most 4096 words");
+        return PTB_OK;
+    }
+    if(s->specSource[which].empty())
+        s->specSource[which] = specializeSource(s->fastHost, which);
+    const int mode = force || specMode() == 1 ? SPEC_WAIT : work >= 67108864.0 ? SPEC_START : SPEC_PEEK;
+    std::string err;
+    const SpecKernels *k = specializeGet(s->specSource[which], s->device, mode, err);
+    if(!k)
+    {
+        if(force)
+            return fail(PTB_ECUDA, "specialised kernels unavailable: " + err);
+        return PTB_OK;
+    }
+    // launch shape: no program in shared memory, pools and start stack only
+    const DevScene &dev = s->dev;
+    CsgConfig &cfg = sp.cfg;
+    cfg.threads = PTB_FAST_THREADS, cfg.fast = 1, cfg.stageProgram = 0;
+    cfg.cap = std::min(dev.poolBound, 12);
+    cfg.smemBytes = fastSharedBytes(dev, cfg.cap, false, 1);
+    if(cfg.smemBytes > s->smemOptin)
+        return PTB_OK;
+    const int perSm = specOccupancy(which == SPEC_TRACE ? k->tracePrimary : k->intersect, cfg.threads, cfg.smemBytes);
+    if(perSm <= 0)
+        return PTB_OK;
+    cfg.blocks = perSm * s->smCount;
+    cfg.ovfStride = (size_t)cfg.blocks * cfg.threads;
+    cfg.overflow = nullptr;
+    if(dev.poolBound > cfg.cap)
+    {
+        CU(s->specOverflow.ensure((size_t)(dev.poolBound - cfg.cap) * 3 * sizeof(float) * cfg.ovfStride));
+        cfg.overflow = (float *)s->specOverflow.p;
+    }
+    sp.k = k;
+    return PTB_OK;
+}
+#define SPEC_LAUNCH(fn, cfg, stream, ...)                                                                  \
+    do                                                                                                     \
+    {                                                                                                      \
+        void *args_[] = {__VA_ARGS__};                                                                     \
+        std::string err_;                                                                                  \
+        if(specLaunch(fn, (cfg).blocks, (cfg).threads, (cfg).smemBytes, stream, args_, err_) != 0)         \
+            return fail(PTB_ECUDA, err_);                                                                  \
+    } while(0)
+
 // ---- ray-batch intersection -----------------------------------------------------------------------
 extern "C" int ptb200_intersect_device(PtbScene *s, const void *d_origins4, const void *d_dirs4, size_t n, void *d_hits, void *d_spans, int max_spans, uint32_t flags,
                                        void *stream)
@@ -970,6 +1067,19 @@ extern "C" int ptb200_intersect_device(PtbScene *s, const void *d_origins4, cons
         return rc;
     if(n == 0)
         return PTB_OK;
+    SpecConfig sp;
+    if(int rc = chooseSpec(s, flags, (double)n, SPEC_INTERSECT, sp))
+        return rc;
+    if(sp.k)
+    {
+        DevScene dev = s->dev;
+        int cap = sp.cfg.cap;
+        float *ovf = sp.cfg.overflow;
+        size_t ovfStride = sp.cfg.ovfStride;
+        SPEC_LAUNCH((flags & PTB_FLAG_ORIGIN0) ? sp.k->intersectO0 : sp.k->intersect, sp.cfg, (cudaStream_t)stream, &dev, &cap, &ovf, &ovfStride, (void *)&d_origins4, (void *)&d_dirs4, &n,
+                    &d_hits, &d_spans, &max_spans);
+        return PTB_OK;
+    }
     launchIntersect(s->dev, cfg, (const float4 *)d_origins4, (const float4 *)d_dirs4, n, (PtbHit *)d_hits, (PtbSpan *)d_spans, max_spans, exact, (flags & PTB_FLAG_ORIGIN0) != 0, (cudaStream_t)stream);
     CU(cudaGetLastError());
     return PTB_OK;
@@ -1012,6 +1122,57 @@ extern "C" int ptb200_intersect(PtbScene *s, const float *origins, const float *
     {
         return fail(PTB_ENOMEM, "out of host memory");
     }
+}
+
+// ---- scene-specialised kernels: inspection -------------------------------------------------------------
+extern "C" int ptb200_specialize_probe(const PtbSceneDesc *desc, int which, char *source, size_t source_capacity, size_t *source_length, size_t *cubin_bytes)
+{
+    try
+    {
+        std::vector<uint4> fast;
+        if(int rc = sceneCreateImpl(desc, nullptr, &fast))
+            return rc;
+        const std::string src = specializeSource(fast, which);
+        if(source_length)
+            *source_length = src.size();
+        if(source && source_capacity)
+        {
+            size_t n = std::min(source_capacity - 1, src.size());
+            memcpy(source, src.data(), n);
+            source[n] = 0;
+        }
+        if(cubin_bytes)
+        {
+            std::vector<char> cubin;
+            std::string log;
+            if(specializeCompile(src, cubin, log) != 0)
+                return fail(PTB_ECUDA, log);
+            *cubin_bytes = cubin.size();
+        }
+        return PTB_OK;
+    }
+    catch(std::bad_alloc &)
+    {
+        return fail(PTB_ENOMEM, "out of host memory");
+    }
+}
+
+extern "C" int ptb200_scene_specialized(PtbScene *s, double *compile_ms, int *passes_specialized, int *passes_total)
+{
+    if(!s)
+        return fail(PTB_EINVAL, "null argument");
+    std::lock_guard<std::mutex> g(s->lock);
+    if(passes_specialized)
+        *passes_specialized = s->lastSpecPasses;
+    if(passes_total)
+        *passes_total = s->lastPasses;
+    if(s->specSource[SPEC_TRACE].empty())
+        return 0;
+    std::string err;
+    const SpecKernels *k = specializeGet(s->specSource[SPEC_TRACE], s->device, SPEC_PEEK, err);
+    if(k && compile_ms)
+        *compile_ms = k->compileMs;
+    return k ? 1 : 0;
 }
 
 // ---- inspection entry points ------------------------------------------------------------------------
@@ -1186,6 +1347,7 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
     pass.seed = p->seed;
     pass.flags = p->flags;
     uint64_t launches = 0;
+    int specPasses = 0;
     for(int i = 0; i < nPasses; i++)
     {
         unsigned *c = (unsigned *)sx.counters.p + (size_t)i * (stages + 1);
@@ -1194,7 +1356,18 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
         cudaEvent_t *ev = timed ? &sx.events[(size_t)i * evPerPass] : nullptr;
         if(timed)
             CU(cudaEventRecord(ev[0], stream));
-        launchTracePrimary(s->dev, cfg, pass, hits, stream);
+        // the specialised kernels may arrive (background compile) between two passes
+        SpecConfig sp;
+        if(int rc = chooseSpec(s, p->flags, (double)nPix * p->spp, SPEC_TRACE, sp))
+            return rc;
+        DevScene devArg = s->dev;
+        if(sp.k)
+        {
+            specPasses++;
+            SPEC_LAUNCH(sp.k->tracePrimary, sp.cfg, stream, &devArg, &sp.cfg.cap, &sp.cfg.overflow, &sp.cfg.ovfStride, &pass, &hits);
+        }
+        else
+            launchTracePrimary(s->dev, cfg, pass, hits, stream);
         if(timed)
             CU(cudaEventRecord(ev[1], stream));
         launchShade(s->dev, shadeBlocks, true, pass, accum, hits, q[0], nullptr, q[0], c, stream);
@@ -1202,7 +1375,14 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
             CU(cudaEventRecord(ev[2], stream));
         for(int b = 1; b <= p->max_depth; b++)
         {
-            launchTraceQueue(s->dev, cfg, q[(b - 1) & 1], c + (b - 1), hits, stream);
+            if(sp.k)
+            {
+                RayQueue qin = q[(b - 1) & 1];
+                const unsigned *cin = c + (b - 1);
+                SPEC_LAUNCH(sp.k->traceQueue, sp.cfg, stream, &devArg, &sp.cfg.cap, &sp.cfg.overflow, &sp.cfg.ovfStride, &qin, &cin, &hits);
+            }
+            else
+                launchTraceQueue(s->dev, cfg, q[(b - 1) & 1], c + (b - 1), hits, stream);
             if(timed)
                 CU(cudaEventRecord(ev[1 + 2 * b], stream));
             launchShade(s->dev, shadeBlocksBounce, false, pass, accum, hits, q[(b - 1) & 1], c + (b - 1), q[b & 1], c + b, stream);
@@ -1227,6 +1407,7 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
     CU(cudaStreamSynchronize(stream));
     memset(stats, 0, sizeof(*stats));
     stats->launches = launches;
+    s->lastSpecPasses = specPasses, s->lastPasses = nPasses;
     for(int i = 0; i < nPasses; i++)
     {
         const unsigned *c = sx.hostCounters + (size_t)i * (stages + 1);

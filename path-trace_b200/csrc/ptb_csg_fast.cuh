@@ -309,13 +309,145 @@ __device__ __forceinline__ void xfDisc(const uint4 &h, const uint4 &u0, const ui
     disc = fmaf(b, b, -(a * cc));
 }
 
+// One plane of a plane record folded into the running {(-inf, loEnd], [upStart, +inf)} pair:
+// PlaneSpanIterator::init, src/plane.cpp:35-63, on a world-space plane u0 = (n.xyz, D).
+template <bool O0>
+__device__ __forceinline__ void planeFold(const uint4 &u0, uint32_t tags, V3 o, V3 d, float &loEnd, float &upStart, uint32_t &loTags, uint32_t &upTags, bool &full)
+{
+    const float nx = __uint_as_float(u0.x), ny = __uint_as_float(u0.y), nz = __uint_as_float(u0.z);
+    float divisor = fmaf(d.x, nx, fmaf(d.y, ny, d.z * nz));
+    float numerator = O0 ? -__uint_as_float(u0.w) : -fmaf(o.x, nx, fmaf(o.y, ny, fmaf(o.z, nz, __uint_as_float(u0.w))));
+    float t = numerator * rcpApprox(divisor);
+    bool parallel = fabsf(divisor) < PTB_EPS * PTB_EPS || !(fabsf(t) < PTB_MAX_VALUE);
+    if(parallel)
+    {
+        if(fabsf(numerator) < PTB_EPS * PTB_EPS)
+            full = true, loTags = upTags = tags; // the ray lies in the plane: the whole line
+    }
+    else if(divisor < 0.0f)
+    { // [t, +inf): the earliest start wins and brings both its tags (src/union.cpp:113-123)
+        if(t <= upStart)
+            upStart = t, upTags = tags;
+    }
+    else
+    { // (-inf, t]: equal starts keep the later operand's start, the larger end its tag (:124-133)
+        loTags = (loTags & 0xFFFF0000u) | (tags & 0xFFFFu);
+        if(t >= loEnd)
+            loEnd = t, loTags = (loTags & 0xFFFFu) | (tags & 0xFFFF0000u);
+    }
+}
+// The folded pair as the record's leaf: nothing, one span, or two spans in order.
+__device__ __forceinline__ void planeFinish(float loEnd, float upStart, uint32_t loTags, uint32_t upTags, bool full, bool &hit, bool &two, float &lt0, float &lt1, float &ut0,
+                                            uint32_t &ltags, uint32_t &utags)
+{
+    const bool hasLo = loEnd > -3.0e38f, hasUp = upStart < 3.0e38f;
+    hit = full || hasLo || hasUp;
+    two = false;
+    lt0 = -PTB_MAX_VALUE, lt1 = PTB_MAX_VALUE, ltags = upTags; // the whole line (a ray in the plane)
+    ut0 = upStart, utags = upTags;
+    if(full)
+        ;
+    else if(loEnd >= upStart) // two planes only: either order gives the whole line (src/union.cpp:113-133)
+        ltags = (loTags & 0xFFFFu) | (upTags & 0xFFFF0000u);
+    else if(hasLo)
+        lt1 = loEnd, ltags = loTags, two = hasUp;
+    else
+        lt0 = upStart;
+}
+// Discriminant of an untransformed sphere: header h = {.., .., -r^2, |c|^2 - r^2}, u0 = (-c.xyz, 0); src/sphere.cpp:33-38.
+template <bool O0>
+__device__ __forceinline__ void sphereDisc(const uint4 &h, const uint4 &u0, V3 o, V3 d, float &a, float &b, float &e)
+{
+    a = fmaf(d.x, d.x, fmaf(d.y, d.y, d.z * d.z));
+    float cc;
+    if(O0)
+    {
+        b = fmaf(__uint_as_float(u0.x), d.x, fmaf(__uint_as_float(u0.y), d.y, __uint_as_float(u0.z) * d.z));
+        cc = __uint_as_float(h.w);
+    }
+    else
+    {
+        float ox = o.x + __uint_as_float(u0.x), oy = o.y + __uint_as_float(u0.y), oz = o.z + __uint_as_float(u0.z);
+        b = fmaf(ox, d.x, fmaf(oy, d.y, oz * d.z));
+        cc = fmaf(ox, ox, fmaf(oy, oy, fmaf(oz, oz, __uint_as_float(h.z))));
+    }
+    e = fmaf(b, b, -(a * cc));
+}
+
+// What one program word does to one ray's operand stack once its leaf (if any) has been evaluated:
+// push the leaf's list (one span; two for a plane cluster) or an empty one, then run the word's
+// operators.  hx = the word's header, see the enum above.
+__device__ __forceinline__ void fastPushOperate(uint32_t hx, bool hit, bool two, float lt0, float lt1, float ut0, uint32_t ltags, uint32_t utags, FastState &st,
+                                                const FastPool &pool)
+{
+    const uint32_t W = 4u * PTB_FAST_THREADS;
+    const bool isLeaf = !(hx & FK_CONTROL);
+    const uint32_t action = (hx >> 4) & 3u, npost = (hx >> 8) & 15u;
+    const bool tail = (hx & (FH_TAIL | FK_CONTROL)) != 0u, isPlane = (hx & FK_PLANE) != 0u;
+    if(!tail && !hit)
+    { // a missed leaf with nothing behind it is an empty list, or nothing at all
+        st.bits <<= (hx >> 6) & 1u;
+        return;
+    }
+    uint32_t first = 0u; // the leaf's action, if it has to run as an operator on two lists
+    if(isLeaf)
+    {
+        if(!hit)
+        {
+            st.bits <<= (hx >> 6) & 1u; // a pushed leaf that missed is an empty list
+            if(action == FA_INTERSECTION && (st.bits & 1u))
+            { // A n {} = {}: a missed leaf drops the spans of the list below
+                st.sp -= W;
+                st.top = (int)lds32(st.sp);
+                st.bits &= ~1u;
+            }
+        }
+        else if(action <= FA_UNION || (st.bits & 1u))
+        { // push the leaf's list ({} \ B and {} n B stay empty: B is never stored)
+            SpanRec s;
+            s.t0 = lt0, s.t1 = lt1, s.tags = ltags;
+            sts32(st.sp, (uint32_t)st.top);
+            pool.store(st.top, s);
+            const bool second = isPlane && two;
+            if(second)
+            {
+                s.t0 = ut0, s.t1 = PTB_MAX_VALUE, s.tags = utags;
+                pool.store(st.top + 1, s);
+            }
+            const bool replaces = action == FA_UNION && !(st.bits & 1u); // {} u B = B: B takes the empty list's entry
+            st.top += second ? 2 : 1, st.sp += W, st.bits = replaces ? st.bits | 1u : (st.bits << 1) | 1u;
+            first = replaces ? 0u : action;
+        }
+    }
+    if(first == 0u)
+    {
+        if(npost == 0u)
+            return;
+        const uint32_t involved = st.bits & ((2u << npost) - 1u);
+        if(PTB_TAIL_CLOSED && (hx & FH_UNION_TAIL) && __popc(involved) <= 1)
+        { // a run of Unions: the lists involved collapse into one; spans move only if two of them have any
+            st.bits = ((st.bits >> npost) & ~1u) | (involved ? 1u : 0u);
+            return;
+        }
+    }
+    uint32_t ops = hx >> 12, left = npost, op = first;
+    if(op == 0u)
+        op = (ops & 3u) + FA_UNION, ops >>= 2, left--;
+    for(;;)
+    {
+        fastOp(pool, op, st);
+        if(left == 0u)
+            break;
+        op = (ops & 3u) + FA_UNION, ops >>= 2, left--;
+    }
+}
+
 // Runs the whole program for R rays per lane, all 32 lanes of the warp together (SKIP words
 // vote).  Ray r's root span list ends up in pool r, slots [0, topOut[r]).  (R = 2 was measured
 // slower than R = 1 on B200 — occupancy beats per-thread ILP here — and is kept for experiments.)
 template <bool GP, bool O0, int R>
 __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restrict__ gprog, const V3 (&o)[R], const V3 (&d)[R], int (&topOut)[R])
 {
-    const uint32_t W = 4u * PTB_FAST_THREADS;
     FastState st[R];
 #pragma unroll
     for(int r = 0; r < R; r++)
@@ -433,46 +565,10 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
             for(;;)
             {
                 const uint4 u0 = PTB_PROG(0);
-                const float nx = __uint_as_float(u0.x), ny = __uint_as_float(u0.y), nz = __uint_as_float(u0.z);
 #pragma unroll
                 for(int r = 0; r < R; r++)
                 {
-                    float divisor = fmaf(d[r].x, nx, fmaf(d[r].y, ny, d[r].z * nz));
-                    float numerator = O0 ? -__uint_as_float(u0.w) : -fmaf(o[r].x, nx, fmaf(o[r].y, ny, fmaf(o[r].z, nz, __uint_as_float(u0.w))));
-                    float t = numerator * rcpApprox(divisor);
-                    bool parallel = fabsf(divisor) < PTB_EPS * PTB_EPS || !(fabsf(t) < PTB_MAX_VALUE);
-#if PTB_PLANE_SELECT
-                    // selects, not branches: the cases differ from lane to lane
-                    const bool inPlane = parallel && fabsf(numerator) < PTB_EPS * PTB_EPS; // the ray lies in the plane: the whole line
-                    const bool upper = !parallel && divisor < 0.0f, lower = !parallel && !(divisor < 0.0f);
-                    // [t, +inf): the earliest start wins and brings both its tags (src/union.cpp:113-123)
-                    const bool newStart = (upper && t <= upStart[r]) || inPlane;
-                    // (-inf, t]: equal starts keep the later operand's start, the larger end its tag (:124-133)
-                    const bool newEnd = (lower && t >= loEnd[r]) || inPlane;
-                    full[r] = full[r] || inPlane;
-                    upStart[r] = newStart && !inPlane ? t : upStart[r];
-                    upTags[r] = newStart ? tags : upTags[r];
-                    loTags[r] = lower || inPlane ? (loTags[r] & 0xFFFF0000u) | (tags & 0xFFFFu) : loTags[r];
-                    loEnd[r] = newEnd && !inPlane ? t : loEnd[r];
-                    loTags[r] = newEnd ? (loTags[r] & 0xFFFFu) | (tags & 0xFFFF0000u) : loTags[r];
-#else
-                    if(parallel)
-                    {
-                        if(fabsf(numerator) < PTB_EPS * PTB_EPS)
-                            full[r] = true, loTags[r] = upTags[r] = tags; // the ray lies in the plane: the whole line
-                    }
-                    else if(divisor < 0.0f)
-                    { // [t, +inf): the earliest start wins and brings both its tags (src/union.cpp:113-123)
-                        if(t <= upStart[r])
-                            upStart[r] = t, upTags[r] = tags;
-                    }
-                    else
-                    { // (-inf, t]: equal starts keep the later operand's start, the larger end its tag (:124-133)
-                        loTags[r] = (loTags[r] & 0xFFFF0000u) | (tags & 0xFFFFu);
-                        if(t >= loEnd[r])
-                            loEnd[r] = t, loTags[r] = (loTags[r] & 0xFFFFu) | (tags & 0xFFFF0000u);
-                    }
-#endif
+                    planeFold<O0>(u0, tags, o[r], d[r], loEnd[r], upStart[r], loTags[r], upTags[r], full[r]);
                 }
                 if(left == 0u)
                 {
@@ -495,21 +591,7 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
             }
 #pragma unroll
             for(int r = 0; r < R; r++)
-            {
-                const bool hasLo = loEnd[r] > -3.0e38f, hasUp = upStart[r] < 3.0e38f;
-                hit[r] = full[r] || hasLo || hasUp;
-                two[r] = false;
-                lt0[r] = -PTB_MAX_VALUE, lt1[r] = PTB_MAX_VALUE, ltags[r] = upTags[r]; // the whole line (a ray in the plane)
-                ut0[r] = upStart[r], utags[r] = upTags[r];
-                if(full[r])
-                    ;
-                else if(loEnd[r] >= upStart[r]) // two planes only: either order gives the whole line (src/union.cpp:113-133)
-                    ltags[r] = (loTags[r] & 0xFFFFu) | (upTags[r] & 0xFFFF0000u);
-                else if(hasLo)
-                    lt1[r] = loEnd[r], ltags[r] = loTags[r], two[r] = hasUp;
-                else
-                    lt0[r] = upStart[r];
-            }
+                planeFinish(loEnd[r], upStart[r], loTags[r], upTags[r], full[r], hit[r], two[r], lt0[r], lt1[r], ut0[r], ltags[r], utags[r]);
             PTB_MISS_EXIT();
         }
         else if(h.x & FK_SPHERE)
@@ -519,20 +601,8 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
 #pragma unroll
             for(int r = 0; r < R; r++)
             {
-                float a = fmaf(d[r].x, d[r].x, fmaf(d[r].y, d[r].y, d[r].z * d[r].z));
-                float b, cc;
-                if(O0)
-                {
-                    b = fmaf(__uint_as_float(u0.x), d[r].x, fmaf(__uint_as_float(u0.y), d[r].y, __uint_as_float(u0.z) * d[r].z));
-                    cc = __uint_as_float(h.w);
-                }
-                else
-                {
-                    float ox = o[r].x + __uint_as_float(u0.x), oy = o[r].y + __uint_as_float(u0.y), oz = o[r].z + __uint_as_float(u0.z);
-                    b = fmaf(ox, d[r].x, fmaf(oy, d[r].y, oz * d[r].z));
-                    cc = fmaf(ox, ox, fmaf(oy, oy, fmaf(oz, oz, __uint_as_float(h.z))));
-                }
-                float e = fmaf(b, b, -(a * cc));
+                float a, b, e;
+                sphereDisc<O0>(h, u0, o[r], d[r], a, b, e);
                 hit[r] = e > PTB_EPS;
                 if(hit[r])
                 { // src/sphere.cpp:44-46
@@ -561,70 +631,9 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
         }
         // ---- the ONE place where lists are pushed and operators run (the code of the three merge
         // state machines exists once in the kernel: the hot loop stays instruction-cache resident) ----
-        const bool isLeaf = !(h.x & FK_CONTROL);
-        const uint32_t action = (h.x >> 4) & 3u, npost = (h.x >> 8) & 15u;
-        const bool tail = (h.x & (FH_TAIL | FK_CONTROL)) != 0u, isPlane = (h.x & FK_PLANE) != 0u;
 #pragma unroll
         for(int r = 0; r < R; r++)
-        {
-            if(!tail && !hit[r])
-            { // a missed leaf with nothing behind it is an empty list, or nothing at all
-                st[r].bits <<= (h.x >> 6) & 1u;
-                continue;
-            }
-            const FastPool pool = c.poolOf(r);
-            uint32_t first = 0u; // the leaf's action, if it has to run as an operator on two lists
-            if(isLeaf)
-            {
-                if(!hit[r])
-                {
-                    st[r].bits <<= (h.x >> 6) & 1u; // a pushed leaf that missed is an empty list
-                    if(action == FA_INTERSECTION && (st[r].bits & 1u))
-                    { // A n {} = {}: a missed leaf drops the spans of the list below
-                        st[r].sp -= W;
-                        st[r].top = (int)lds32(st[r].sp);
-                        st[r].bits &= ~1u;
-                    }
-                }
-                else if(action <= FA_UNION || (st[r].bits & 1u))
-                { // push the leaf's list ({} \ B and {} n B stay empty: B is never stored)
-                    SpanRec s;
-                    s.t0 = lt0[r], s.t1 = lt1[r], s.tags = ltags[r];
-                    sts32(st[r].sp, (uint32_t)st[r].top);
-                    pool.store(st[r].top, s);
-                    const bool second = isPlane && two[r];
-                    if(second)
-                    {
-                        s.t0 = ut0[r], s.t1 = PTB_MAX_VALUE, s.tags = utags[r];
-                        pool.store(st[r].top + 1, s);
-                    }
-                    const bool replaces = action == FA_UNION && !(st[r].bits & 1u); // {} u B = B: B takes the empty list's entry
-                    st[r].top += second ? 2 : 1, st[r].sp += W, st[r].bits = replaces ? st[r].bits | 1u : (st[r].bits << 1) | 1u;
-                    first = replaces ? 0u : action;
-                }
-            }
-            if(first == 0u)
-            {
-                if(npost == 0u)
-                    continue;
-                const uint32_t involved = st[r].bits & ((2u << npost) - 1u);
-                if(PTB_TAIL_CLOSED && (h.x & FH_UNION_TAIL) && __popc(involved) <= 1)
-                { // a run of Unions: the lists involved collapse into one; spans move only if two of them have any
-                    st[r].bits = ((st[r].bits >> npost) & ~1u) | (involved ? 1u : 0u);
-                    continue;
-                }
-            }
-            uint32_t ops = h.x >> 12, left = npost, op = first;
-            if(op == 0u)
-                op = (ops & 3u) + FA_UNION, ops >>= 2, left--;
-            for(;;)
-            {
-                fastOp(pool, op, st[r]);
-                if(left == 0u)
-                    break;
-                op = (ops & 3u) + FA_UNION, ops >>= 2, left--;
-            }
-        }
+            fastPushOperate(h.x, hit[r], two[r], lt0[r], lt1[r], ut0[r], ltags[r], utags[r], st[r], c.poolOf(r));
     }
 #undef PTB_PROG
 #undef PTB_ADVANCE

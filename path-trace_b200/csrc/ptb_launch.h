@@ -1,8 +1,10 @@
 // ptb_launch.h — internal interface between the C-ABI host code (ptb_capi.cu) and the kernels
 // (ptb_kernels.cu).  Not part of the public boundary.
 #pragma once
+#ifndef __CUDACC_RTC__
 #include <cuda_runtime.h>
 #include <stdint.h>
+#endif
 
 #include "ptb_scene_dev.cuh"
 
@@ -34,6 +36,7 @@ struct RayQueue
 struct FastDivisor
 {
     uint32_t d, m, shift;
+#ifndef __CUDACC_RTC__
     static FastDivisor make(uint32_t d)
     {
         FastDivisor f;
@@ -48,6 +51,7 @@ struct FastDivisor
         }
         return f;
     }
+#endif
 #ifdef __CUDACC__
     __device__ __forceinline__ uint32_t div(uint32_t n) const
     {
@@ -77,6 +81,7 @@ struct RenderPass
     const uint32_t *pixelList;
 };
 
+#ifndef __CUDACC_RTC__ /* host-side launchers: not seen by the run-time compiled device code */
 void launchIntersect(const DevScene &sc, const CsgConfig &cfg, const float4 *origins, const float4 *dirs, size_t n, PtbHit *hits, PtbSpan *spans, int maxSpans,
                      bool exact, bool origin0, cudaStream_t stream);
 // Trace stage of the first wavefront level: camera rays for rw*rh*samplesThisPass samples -> hits[i].
@@ -120,6 +125,7 @@ double launchFmaPeak(int blocks, int threads, int iters, cudaStream_t stream);
 size_t csgSharedBytes(const DevScene &sc, int threads, int cap, bool stageProgram);
 size_t fastSharedBytes(const DevScene &sc, int cap, bool stageProgram, int rays);
 int traceRaysPerThread(); // rays each thread of the trace kernels carries
+#endif
 
 } // namespace ptb
 
@@ -127,5 +133,7 @@ namespace ptb
 {
 // which: 0 = intersect (fast), 1 = intersect (exact), 2 = render stages; globalProgram: the
 // program stream is too large for shared memory and is read through the read-only cache
+#ifndef __CUDACC_RTC__
 int csgBlocksPerSm(int which, int threads, size_t smemBytes, bool globalProgram);
+#endif
 }

@@ -9,8 +9,10 @@
 //                       reciprocal / rsqrt; relative error ~1e-7..1e-6, inside the 1e-5 gate of
 //                       BASELINE.json.  This is the policy the renderer runs.
 #pragma once
+#ifndef __CUDACC_RTC__
 #include <cuda_runtime.h>
 #include <stdint.h>
+#endif
 
 namespace ptb
 {

@@ -76,4 +76,24 @@ __device__ __forceinline__ V3 boundaryNormal(const DevScene &sc, uint32_t tag, f
     return (tag & 1u) ? neg(n) : n;
 }
 
+// ---- path state -----------------------------------------------------------------------------
+struct PathState
+{
+    V3 o, d;         // current ray (direction NOT normalised)
+    V3 thr;          // product of branch weights so far
+    float strength;  // the reference's `strength` argument
+    uint32_t pixel;  // y * width + x
+    uint32_t sample; // global camera-sample index
+    uint32_t depth;  // the reference's `depth` argument for this ray
+    uint32_t rngBlock;
+};
+
+struct Hit
+{
+    float t;
+    V3 n;      // faces against the ray
+    int mat;
+    float ior; // relative ior across the boundary
+};
+
 } // namespace ptb

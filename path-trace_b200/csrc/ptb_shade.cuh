@@ -111,25 +111,6 @@ __device__ __forceinline__ bool scatterCap(Philox &rng, V3 n, V3 r, float sc, V3
     return true;
 }
 
-// ---- path state -----------------------------------------------------------------------------
-struct PathState
-{
-    V3 o, d;         // current ray (direction NOT normalised)
-    V3 thr;          // product of branch weights so far
-    float strength;  // the reference's `strength` argument
-    uint32_t pixel;  // y * width + x
-    uint32_t sample; // global camera-sample index
-    uint32_t depth;  // the reference's `depth` argument for this ray
-    uint32_t rngBlock;
-};
-
-struct Hit
-{
-    float t;
-    V3 n;      // faces against the ray
-    int mat;
-    float ior; // relative ior across the boundary
-};
 
 // Shades one hit.  Adds thr*emissive to `radiance`.  Returns true when the path continues
 // (ps then holds the next ray), false when it ends here.

@@ -1,0 +1,427 @@
+// ptb_specialize.cu — scene-specialised trace kernels: the compiled fast stream of ONE scene printed
+// as straight-line CUDA, compiled at run time with NVRTC for sm_100a and loaded through the driver API.
+// Host code only.  libnvrtc and libcuda are dlopen()ed on first use, so libptb200.so still loads (and
+// fails loudly with PTB_ENODEV) on a machine without a driver; when either is missing or the compile
+// fails the renderer keeps the interpreting kernels — same results, more instructions per ray.
+#include <dlfcn.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <chrono>
+#include <map>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "ptb_specialize.h"
+#include "ptb_csg_fast.cuh"
+
+#include "ptb_embedded.inc" // kEmbeddedNames[], kEmbeddedSources[], kEmbeddedCount: the device headers as strings
+
+namespace ptb
+{
+
+namespace
+{
+// ---- the two libraries ------------------------------------------------------------------------------
+typedef int (*nvrtcCreateProgram_t)(void **, const char *, const char *, int, const char *const *, const char *const *);
+typedef int (*nvrtcCompileProgram_t)(void *, int, const char *const *);
+typedef int (*nvrtcGetSize_t)(void *, size_t *);
+typedef int (*nvrtcGetData_t)(void *, char *);
+typedef int (*nvrtcDestroyProgram_t)(void **);
+typedef int (*cuModuleLoadData_t)(void **, const void *);
+typedef int (*cuModuleGetFunction_t)(void **, void *, const char *);
+typedef int (*cuLaunchKernel_t)(void *, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, void *, void **, void **);
+typedef int (*cuFuncSetAttribute_t)(void *, int, int);
+typedef int (*cuFuncGetAttribute_t)(int *, int, void *);
+typedef int (*cuOccupancy_t)(int *, void *, int, size_t);
+typedef int (*cuGetErrorString_t)(int, const char **);
+
+struct Libs
+{
+    bool tried = false, ok = false, triedDriver = false, okDriver = false;
+    std::string why;
+    nvrtcCreateProgram_t nvrtcCreateProgram;
+    nvrtcCompileProgram_t nvrtcCompileProgram;
+    nvrtcGetSize_t nvrtcGetCUBINSize, nvrtcGetProgramLogSize;
+    nvrtcGetData_t nvrtcGetCUBIN, nvrtcGetProgramLog;
+    nvrtcDestroyProgram_t nvrtcDestroyProgram;
+    cuModuleLoadData_t cuModuleLoadData;
+    cuModuleGetFunction_t cuModuleGetFunction;
+    cuLaunchKernel_t cuLaunchKernel;
+    cuFuncSetAttribute_t cuFuncSetAttribute;
+    cuFuncGetAttribute_t cuFuncGetAttribute;
+    cuOccupancy_t cuOccupancy;
+    cuGetErrorString_t cuGetErrorString;
+};
+Libs g_libs;
+std::mutex g_lock;
+
+#define SYM(lib, field, name)                                                                          \
+    if(!(g_libs.field = (decltype(g_libs.field))dlsym(lib, name)))                                     \
+    {                                                                                                  \
+        g_libs.why = std::string("missing symbol ") + name;                                            \
+        return false;                                                                                  \
+    }
+// NVRTC alone is enough to compile (no GPU, no driver needed)
+bool loadNvrtc()
+{
+    if(g_libs.tried)
+        return g_libs.ok;
+    g_libs.tried = true;
+    void *rtc = nullptr;
+    for(const char *name : {"libnvrtc.so.12", "libnvrtc.so", "/usr/local/cuda/lib64/libnvrtc.so.12"})
+        if((rtc = dlopen(name, RTLD_NOW | RTLD_GLOBAL)))
+            break;
+    if(!rtc)
+    {
+        g_libs.why = "libnvrtc.so.12 not found";
+        return false;
+    }
+    SYM(rtc, nvrtcCreateProgram, "nvrtcCreateProgram")
+    SYM(rtc, nvrtcCompileProgram, "nvrtcCompileProgram")
+    SYM(rtc, nvrtcGetCUBINSize, "nvrtcGetCUBINSize")
+    SYM(rtc, nvrtcGetCUBIN, "nvrtcGetCUBIN")
+    SYM(rtc, nvrtcGetProgramLogSize, "nvrtcGetProgramLogSize")
+    SYM(rtc, nvrtcGetProgramLog, "nvrtcGetProgramLog")
+    SYM(rtc, nvrtcDestroyProgram, "nvrtcDestroyProgram")
+    g_libs.ok = true;
+    return true;
+}
+bool loadDriver()
+{
+    if(g_libs.triedDriver)
+        return g_libs.okDriver;
+    g_libs.triedDriver = true;
+    void *cu = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+    if(!cu)
+    {
+        g_libs.why = "libcuda.so.1 not found";
+        return false;
+    }
+    SYM(cu, cuModuleLoadData, "cuModuleLoadData")
+    SYM(cu, cuModuleGetFunction, "cuModuleGetFunction")
+    SYM(cu, cuLaunchKernel, "cuLaunchKernel")
+    SYM(cu, cuFuncSetAttribute, "cuFuncSetAttribute")
+    SYM(cu, cuFuncGetAttribute, "cuFuncGetAttribute")
+    SYM(cu, cuOccupancy, "cuOccupancyMaxActiveBlocksPerMultiprocessor")
+    SYM(cu, cuGetErrorString, "cuGetErrorString")
+    g_libs.okDriver = true;
+    return true;
+}
+#undef SYM
+
+std::string hex(uint32_t v)
+{
+    char buf[16];
+    snprintf(buf, sizeof(buf), "0x%08xu", v);
+    return buf;
+}
+std::string u4(const uint4 &v) { return "make_uint4(" + hex(v.x) + ", " + hex(v.y) + ", " + hex(v.z) + ", " + hex(v.w) + ")"; }
+std::string label(size_t w) { return "W" + std::to_string(w); }
+
+} // namespace
+
+// One labelled block per record of the fast stream (formats: ptb_csg_fast.cuh, compileFastProgram in
+// ptb_capi.cu).  Every block is the body of one trip of evalFast's loop with the record's words as
+// literals; PTB_ADVANCE becomes fall-through or goto.
+std::string specializeSource(const std::vector<uint4> &prog, int which)
+{
+    std::string s;
+    s += "#include \"ptb200.h\"\n#include \"ptb_csg_spec.cuh\"\nnamespace ptb\n{\n";
+    s += "template <bool O0>\n__device__ __forceinline__ void evalSpec(const FastCtx &c, const V3 o, const V3 d, int &topOut)\n{\n";
+    s += "    FastState st;\n    st.bits = 0u, st.top = 0, st.sp = c.stk;\n";
+    s += "    bool hit = false, two = false;\n    float lt0 = 0.f, lt1 = 0.f, ut0 = 0.f, a = 0.f, b = 0.f, e = 0.f;\n    uint32_t ltags = 0u, utags = 0u;\n";
+    size_t pairSecond = (size_t)-1; // record that a pair block may enter with its discriminant computed
+    for(size_t w = 0; w < prog.size();)
+    {
+        const uint4 h = prog[w];
+        const std::string HX = hex(h.x);
+        s += label(w) + ":\n";
+        if(h.x & FK_SPHERE_XF)
+        {
+            const std::string disc = "xfDisc<O0>(" + u4(h) + ", " + u4(prog[w + 1]) + ", " + u4(prog[w + 2]) + ", " + u4(prog[w + 3]) + ", o, d, ";
+            const std::string push = "    specSphere(" + HX + ", " + hex(h.y) + ", a, b, e, st);\n";
+            if(h.x & FH_PAIR)
+            { // both discriminants together; when no ray of the warp hits the first, the second is this trip's leaf
+                const uint4 g = prog[w + 4];
+                s += "    {\n        float a1, b1, e1;\n        " + disc + "a, b, e);\n";
+                s += "        xfDisc<O0>(" + u4(g) + ", " + u4(prog[w + 5]) + ", " + u4(prog[w + 6]) + ", " + u4(prog[w + 7]) + ", o, d, a1, b1, e1);\n";
+                s += "        if(!__any_sync(0xFFFFFFFFu, e > PTB_EPS))\n        {\n            st.bits <<= " + std::to_string((h.x >> 6) & 1u) + "u;\n";
+                s += "            a = a1, b = b1, e = e1;\n            goto " + label(w + 4) + "_have;\n        }\n    }\n";
+                s += push;
+                pairSecond = w + 4;
+            }
+            else
+            {
+                s += "    " + disc + "a, b, e);\n";
+                if(w == pairSecond)
+                    s += label(w) + "_have:\n"; // entered with a, b, e already computed by the pair before
+                s += "    if(specMissExit(" + HX + ", e > PTB_EPS, st))\n        goto " + label(w + 4) + ";\n" + push;
+            }
+            w += 4;
+        }
+        else if(h.x & FK_PLANE)
+        {
+            const uint32_t k = h.z, len = 2u + 2u * k, after = (uint32_t)w + len + (k ? h.w : 0u);
+            s += "    {\n        float loEnd = -3.0e38f, upStart = 3.0e38f;\n        uint32_t loTags = 0u, upTags = 0u;\n        bool full = false;\n";
+            s += "        planeFold<O0>(" + u4(prog[w + 1]) + ", " + hex(h.y) + ", o, d, loEnd, upStart, loTags, upTags, full);\n";
+            for(uint32_t j = 0; j < k; j++)
+                s += "        planeFold<O0>(" + u4(prog[w + 3 + 2 * j]) + ", " + hex(prog[w + 2 + 2 * j].x) + ", o, d, loEnd, upStart, loTags, upTags, full);\n";
+            if(k)
+                s += std::string("        if(!__all_sync(0xFFFFFFFFu, !full && (") + (k == 1u ? "true" : "loEnd < upStart") + ")))\n            goto " + label(w + len) +
+                     "; // the subtree's own words\n";
+            s += "        planeFinish(loEnd, upStart, loTags, upTags, full, hit, two, lt0, lt1, ut0, ltags, utags);\n    }\n";
+            s += "    if(specMissExit(" + HX + ", hit, st))\n        goto " + label(after) + ";\n";
+            s += "    specPushOperate(" + HX + ", hit, two, lt0, lt1, ut0, ltags, utags, st);\n";
+            if(after != w + len)
+                s += "    goto " + label(after) + ";\n";
+            w += len;
+        }
+        else if(h.x & FK_SPHERE)
+        {
+            s += "    sphereDisc<O0>(" + u4(h) + ", " + u4(prog[w + 1]) + ", o, d, a, b, e);\n";
+            s += "    if(specMissExit(" + HX + ", e > PTB_EPS, st))\n        goto " + label(w + 2) + ";\n";
+            s += "    specSphere(" + HX + ", " + hex(h.y) + ", a, b, e, st);\n";
+            w += 2;
+        }
+        else
+        {
+            const uint32_t sub = (h.x >> 4) & 3u;
+            if(sub == 0u)
+                s += "    goto WEND;\n";
+            else if(sub == 1u)
+                s += "    specPushOperate(" + HX + ", false, false, 0.f, 0.f, 0.f, 0u, 0u, st);\n";
+            else
+                s += "    if(!__any_sync(0xFFFFFFFFu, (st.bits & 1u) != 0u))\n        goto " + label(w + 1 + h.y) + ";\n";
+            w += 1;
+        }
+    }
+    s += "WEND:\n    topOut = st.top;\n}\n} // namespace ptb\n";
+    s += "#define PTB_EVAL(GP, O0, R, cx, gprog, o, d, tops) evalSpec<O0>(cx, o[0], d[0], tops[0])\n";
+    // (PTB_TRACE_TRIP_SYNC = __syncthreads() keeps the four warps of a CTA in step through the straight-line
+    // code: measured -20 % on the C4 camera-ray kernel, whose 54 KB of code thrash the instruction cache,
+    // +3 % on C5, whose code fits; large programs are not specialised at all, so it stays off)
+    if(getenv("PTB_SPEC_TRIP_SYNC"))
+        s += "#define PTB_TRACE_TRIP_SYNC() __syncthreads()\n";
+    s += "#include \"ptb_trace.cuh\"\n";
+    if(which == SPEC_TRACE)
+    {
+        s += "extern \"C\" __global__ void __launch_bounds__(PTB_FAST_THREADS, PTB_TRACE_MIN_CTAS) ptbSpecTracePrimary(ptb::DevScene sc, int cap, float *overflow, size_t ovfStride, "
+             "ptb::RenderPass pass, uint2 *hits)\n{\n    ptb::specSharedInit(cap, overflow, ovfStride);\n    ptb::tracePrimaryBody<true>(sc, cap, overflow, ovfStride, pass, hits);\n}\n";
+        s += "extern \"C\" __global__ void __launch_bounds__(PTB_FAST_THREADS, PTB_TRACE_MIN_CTAS) ptbSpecTraceQueue(ptb::DevScene sc, int cap, float *overflow, size_t ovfStride, "
+             "ptb::RayQueue in, const unsigned *inCount, uint2 *hits)\n{\n    ptb::specSharedInit(cap, overflow, ovfStride);\n    ptb::traceQueueBody<true>(sc, cap, overflow, ovfStride, in, inCount, hits);\n}\n";
+    }
+    else
+        for(int o0 = 0; o0 < 2; o0++)
+            s += std::string("extern \"C\" __global__ void __launch_bounds__(PTB_FAST_THREADS) ptbSpecIntersect") + (o0 ? "O0" : "") +
+                 "(ptb::DevScene sc, int cap, float *overflow, size_t ovfStride, const float4 *origins, const float4 *dirs, size_t n, PtbHit *hits, PtbSpan *spans, int maxSpans)\n{\n"
+                 "    ptb::specSharedInit(cap, overflow, ovfStride);\n    ptb::intersectFastBody<true, " +
+                 (o0 ? "true" : "false") + ">(sc, cap, overflow, ovfStride, origins, dirs, n, hits, spans, maxSpans);\n}\n";
+    return s;
+}
+
+int specializeCompile(const std::string &source, std::vector<char> &cubin, std::string &log)
+{
+    std::lock_guard<std::mutex> g(g_lock);
+    if(!loadNvrtc())
+    {
+        log = g_libs.why;
+        return -1;
+    }
+    void *prog = nullptr;
+    int rc = g_libs.nvrtcCreateProgram(&prog, source.c_str(), "ptb_scene.cu", kEmbeddedCount, kEmbeddedSources, kEmbeddedNames);
+    if(rc != 0)
+    {
+        log = "nvrtcCreateProgram failed (" + std::to_string(rc) + ")";
+        return -1;
+    }
+    // -lineinfo (for ncu source pages) costs compile time: only on request.  --split-compile=0: the four
+    // kernels are optimised on as many threads as the host has.
+    std::vector<const char *> opts = {"--gpu-architecture=sm_100a", "-std=c++17", "--split-compile=0"};
+    if(getenv("PTB_SPEC_LINEINFO"))
+        opts.push_back("-lineinfo");
+    rc = g_libs.nvrtcCompileProgram(prog, (int)opts.size(), opts.data());
+    size_t n = 0;
+    if(g_libs.nvrtcGetProgramLogSize(prog, &n) == 0 && n > 1)
+    {
+        log.resize(n);
+        g_libs.nvrtcGetProgramLog(prog, &log[0]);
+    }
+    if(rc != 0)
+    {
+        log = "NVRTC compile failed (" + std::to_string(rc) + "): " + log;
+        g_libs.nvrtcDestroyProgram(&prog);
+        return -1;
+    }
+    n = 0;
+    g_libs.nvrtcGetCUBINSize(prog, &n);
+    cubin.resize(n);
+    g_libs.nvrtcGetCUBIN(prog, cubin.data());
+    g_libs.nvrtcDestroyProgram(&prog);
+    if(const char *dump = getenv("PTB_SPEC_DUMP"))
+        if(FILE *f = fopen(dump, "wb"))
+        { // for cuobjdump -sass / -res-usage
+            fwrite(cubin.data(), 1, cubin.size(), f);
+            fclose(f);
+        }
+    return cubin.empty() ? -1 : 0;
+}
+
+static std::string cuError(int rc)
+{
+    const char *msg = nullptr;
+    if(g_libs.cuGetErrorString && g_libs.cuGetErrorString(rc, &msg) == 0 && msg)
+        return msg;
+    return "CUDA driver error " + std::to_string(rc);
+}
+
+// ---- cache: one entry per distinct generated source, compiled once per process ------------------------
+namespace
+{
+struct Entry
+{
+    int state = 0; // 0 compiling, 1 cubin ready, 2 failed
+    std::vector<char> cubin;
+    std::string log;
+    double compileMs = 0.0;
+    std::map<int, SpecKernels *> loaded; // per device
+};
+// never destroyed: a compile thread may still be running when the process exits
+std::mutex &cacheLock()
+{
+    static std::mutex *m = new std::mutex();
+    return *m;
+}
+std::map<std::string, Entry *> &cache()
+{
+    static std::map<std::string, Entry *> *c = new std::map<std::string, Entry *>();
+    return *c;
+}
+void compileEntry(Entry *e, std::string source)
+{
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<char> cubin;
+    std::string log;
+    int rc = specializeCompile(source, cubin, log);
+    std::lock_guard<std::mutex> g(cacheLock());
+    e->compileMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    e->log = log;
+    e->cubin.swap(cubin);
+    e->state = rc == 0 ? 1 : 2;
+}
+} // namespace
+
+const SpecKernels *specializeGet(const std::string &source, int device, int mode, std::string &err)
+{
+    Entry *e = nullptr;
+    bool compileHere = false;
+    {
+        std::lock_guard<std::mutex> g(cacheLock());
+        auto it = cache().find(source);
+        if(it != cache().end())
+            e = it->second;
+        else if(mode != SPEC_PEEK)
+        {
+            e = new Entry();
+            cache()[source] = e;
+            if(mode == SPEC_START)
+                std::thread(compileEntry, e, source).detach();
+            else
+                compileHere = true;
+        }
+    }
+    if(!e)
+        return nullptr;
+    if(compileHere)
+        compileEntry(e, source);
+    if(mode == SPEC_WAIT)
+        for(;;)
+        { // somebody else's compile: wait for it
+            {
+                std::lock_guard<std::mutex> g(cacheLock());
+                if(e->state != 0)
+                    break;
+            }
+            std::this_thread::sleep_for(std::chrono::milliseconds(5));
+        }
+    std::lock_guard<std::mutex> g(cacheLock());
+    if(e->state == 0)
+        return nullptr; // still compiling: the caller keeps the interpreter for now
+    if(e->state == 2)
+    {
+        err = e->log;
+        return nullptr;
+    }
+    auto it = e->loaded.find(device);
+    if(it != e->loaded.end())
+    {
+        if(!it->second)
+            err = "loading the specialised kernels failed before on this device";
+        return it->second;
+    }
+    // first use on this device: load the cubin into the current (primary) context
+    SpecKernels *k = nullptr;
+    void *module = nullptr;
+    if(!loadDriver())
+    {
+        err = g_libs.why;
+        e->loaded[device] = nullptr;
+        return nullptr;
+    }
+    int rc = g_libs.cuModuleLoadData(&module, e->cubin.data());
+    if(rc != 0)
+        err = "cuModuleLoadData: " + cuError(rc);
+    else
+    {
+        k = new SpecKernels();
+        k->module = module;
+        struct
+        {
+            void **fn;
+            const char *name;
+        } want[] = {{&k->tracePrimary, "ptbSpecTracePrimary"}, {&k->traceQueue, "ptbSpecTraceQueue"}, {&k->intersect, "ptbSpecIntersect"}, {&k->intersectO0, "ptbSpecIntersectO0"}};
+        for(auto &x : want)
+            if(g_libs.cuModuleGetFunction(x.fn, module, x.name) != 0)
+                *x.fn = nullptr; // the other program holds this one
+        if(!k->tracePrimary && !k->intersect)
+        {
+            err = "the compiled module holds none of the expected kernels";
+            delete k;
+            k = nullptr;
+        }
+        if(k)
+        {
+            g_libs.cuFuncGetAttribute(&k->regsTrace, 4 /* CU_FUNC_ATTRIBUTE_NUM_REGS */, k->tracePrimary ? k->tracePrimary : k->intersect);
+            k->cubinBytes = e->cubin.size();
+            k->compileMs = e->compileMs;
+        }
+    }
+    e->loaded[device] = k; // failures are remembered too: no retry storm
+    return k;
+}
+
+int specOccupancy(void *fn, int threads, size_t smemBytes)
+{
+    int n = 0;
+    if(smemBytes > 48 * 1024 && g_libs.cuFuncSetAttribute(fn, 8 /* CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES */, (int)smemBytes) != 0)
+        return 0;
+    if(g_libs.cuOccupancy(&n, fn, threads, smemBytes) != 0)
+        return 0;
+    return n;
+}
+
+int specLaunch(void *fn, int blocks, int threads, size_t smemBytes, cudaStream_t stream, void **args, std::string &err)
+{
+    int rc = g_libs.cuLaunchKernel(fn, (unsigned)blocks, 1, 1, (unsigned)threads, 1, 1, (unsigned)smemBytes, (void *)stream, args, nullptr);
+    if(rc != 0)
+    {
+        err = "cuLaunchKernel: " + cuError(rc);
+        return -1;
+    }
+    return 0;
+}
+
+} // namespace ptb

@@ -120,11 +120,30 @@ class DeviceScene:
         check(capi.product().ptb200_render_adaptive(self.handle, C.byref(params), C.byref(ap), out.ctypes.data, source.ctypes.data, lattice.ctypes.data, C.byref(stats), C.byref(astats)))
         return out, source, lattice, stats, astats
 
+    def specialized(self):
+        """ptb200_scene_specialized: (kernels ready?, compile ms, passes of the last stats render that ran them, passes)."""
+        ms, a, b = C.c_double(), C.c_int(), C.c_int()
+        rc = capi.product().ptb200_scene_specialized(self.handle, C.byref(ms), C.byref(a), C.byref(b))
+        if rc < 0:
+            check(rc)
+        return rc == 1, ms.value, a.value, b.value
+
     def render_accumulate(self, params, accum, stream=None, want_stats=True):
         """Adds this call's radiance sums into a device (H, W, 4) float32 torch tensor."""
         stats = PtbStats()
         check(capi.product().ptb200_render_accumulate_device(self.handle, C.byref(params), accum.data_ptr(), C.byref(stats) if want_stats else None, stream))
         return stats
+
+
+def specialize_probe(flat, which=0, compile=True):
+    """ptb200_specialize_probe (no GPU needed): the CUDA source generated for a flattened scene and, with
+    compile, the size of the sm_100a cubin NVRTC makes of it."""
+    lib = capi.product()
+    n, cubin = C.c_size_t(), C.c_size_t()
+    check(lib.ptb200_specialize_probe(C.byref(flat.desc), which, None, 0, C.byref(n), None))
+    buf = C.create_string_buffer(n.value + 1)
+    check(lib.ptb200_specialize_probe(C.byref(flat.desc), which, buf, len(buf), C.byref(n), C.byref(cubin) if compile else None))
+    return buf.value.decode(), cubin.value
 
 
 def resolve(accum, rgba, stream=None):

@@ -1,0 +1,98 @@
+"""Scene-specialised trace kernels (path-trace_b200/csrc/ptb_specialize.cu): the compiled CSG stream of a
+scene printed as straight-line CUDA and compiled with NVRTC at run time.  They must compute exactly what
+the interpreting kernels compute: same device functions, program words as literals.
+
+CPU: the generated source compiles for sm_100a (NVRTC needs no GPU).  GPU: bitwise identity with the
+interpreter on ray batches (hits and whole span lists) and on rendered frames (ray counts; pixels up to
+the order of the float atomics)."""
+import time
+
+import numpy as np
+import pytest
+
+import golden_cases as gc
+from ptb200 import capi, device, scenes
+from ptb200.builder import product_builder
+
+SPEC, INTERP = capi.PTB_FLAG_SPECIALIZE, capi.PTB_FLAG_INTERPRET
+
+
+def test_generated_source_compiles_for_sm100a():
+    b = product_builder()
+    for world, which in ((scenes.config5(b), 0), (scenes.config3(b), 1), (scenes.random_tree(b, 7, 9), 0)):
+        flat = device.Flat(world)
+        source, cubin = device.specialize_probe(flat, which)
+        assert "evalSpec" in source and "W0:" in source and "goto WEND;" in source
+        assert ("ptbSpecTracePrimary" in source) == (which == 0) and ("ptbSpecIntersectO0" in source) == (which == 1)
+        assert cubin > 10000
+    # every record of the stream has its block: one label per leaf and control word
+    flat = device.Flat(scenes.config4(b))
+    source, _ = device.specialize_probe(flat, 0, compile=False)
+    assert source.count("xfDisc<O0>") >= 48 and source.count("planeFold<O0>") >= 22
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["c3", "c4_camera", "c5", "fuzz11", "fuzz12", "fuzz13"])
+def test_specialised_ray_batches_equal_the_interpreter_bitwise(case):
+    b = product_builder()
+    flags = 0
+    if case == "c3":
+        world = scenes.config3(b)
+        o, d = scenes.config3_rays(1 << 18)
+    elif case == "c4_camera":
+        world = scenes.config4(b)
+        rs = np.random.RandomState(4)
+        n = 1 << 17
+        d = np.stack([(rs.rand(n) * 2 - 1) * 3840, (rs.rand(n) * 2 - 1) * 2160, np.full(n, -4320.0)], 1).astype(np.float32)
+        o = np.zeros_like(d)
+        flags = capi.PTB_FLAG_ORIGIN0
+    elif case == "c5":
+        world = scenes.config5(b)
+        o, d = scenes.fuzz_rays(1 << 17, 55)
+    else:
+        seed = int(case[4:])
+        world = scenes.random_tree(b, seed, 6 + seed % 7)
+        o, d = scenes.fuzz_rays(1 << 16, seed)
+    scene = device.DeviceScene(device.Flat(world))
+    h0, s0 = scene.intersect(o, d, 8, flags | INTERP)
+    h1, s1 = scene.intersect(o, d, 8, flags | SPEC)
+    assert h0.tobytes() == h1.tobytes()
+    assert s0.tobytes() == s1.tobytes()
+    assert (h0["kind"] != 0).any()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["c2", "c4", "c5"])
+def test_specialised_render_equals_the_interpreter(name):
+    b = product_builder()
+    world = {"c2": scenes.config2, "c4": scenes.config4, "c5": scenes.config5}[name](b)
+    scene = device.DeviceScene(device.Flat(world))
+    p0 = device.default_params(192, 108, 32, flags=INTERP)
+    p1 = device.default_params(192, 108, 32, flags=SPEC)
+    img0, st0 = scene.render(p0)
+    assert scene.specialized()[2] == 0
+    img1, st1 = scene.render(p1)
+    ready, ms, spec_passes, passes = scene.specialized()
+    assert ready and spec_passes == passes > 0
+    assert (st0.rays, st0.paths, st0.rays_bounce) == (st1.rays, st1.paths, st1.rays_bounce)
+    # same paths, same contributions; only the order of the float atomicAdds per pixel differs
+    np.testing.assert_allclose(img1, img0, rtol=2e-5, atol=1e-6)
+
+
+@pytest.mark.gpu
+def test_background_compile_switches_over_without_changing_the_image():
+    """Default policy: a large render starts the compile on a background thread and keeps interpreting;
+    later passes / frames run the specialised kernels.  The images agree."""
+    b = product_builder()
+    scene = device.DeviceScene(device.Flat(scenes.random_tree(b, 99, 8)))
+    params = device.default_params(1024, 1024, 64, samples_per_pass=4)  # 2^26 paths, 16 passes
+    ref, _ = scene.render(device.default_params(1024, 1024, 64, samples_per_pass=4, flags=INTERP))
+    img, _ = scene.render(params)
+    deadline = time.time() + 120
+    while not scene.specialized()[0] and time.time() < deadline:
+        time.sleep(0.2)
+    assert scene.specialized()[0], "the background compile never finished"
+    img2, _ = scene.render(params)
+    assert scene.specialized()[2] == scene.specialized()[3] > 0
+    np.testing.assert_allclose(img, ref, rtol=2e-5, atol=1e-6)
+    np.testing.assert_allclose(img2, ref, rtol=2e-5, atol=1e-6)

@@ -16,6 +16,6 @@ import json;d=json.load(open('$O/bench_${w}_$TAG.json'));print('$w',round(d['val
 # ncu: launch list of a short run of the same command (16 spp so the list is bounded), then full captures
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/launches_c5_$TAG.csv python bench.py --steps 1 --warmup 1 --spp 16 --no-cpu > $O/ncu_list_$TAG.log 2>&1
 for w in c5 c4; do
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'trace|shadeKernel' -c 4 -o $O/full_${w}_$TAG -f python bench.py --workload $w --steps 1 --warmup 0 --spp 8 --no-cpu > $O/ncu_full_${w}_$TAG.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'race|shadeKernel' -c 4 -o $O/full_${w}_$TAG -f python bench.py --workload $w --steps 1 --warmup 0 --spp 8 --no-cpu > $O/ncu_full_${w}_$TAG.log 2>&1
 done
 ls -la $O | tail -n 20
