@@ -300,6 +300,22 @@ std::map<std::string, Entry *> &cache()
     static std::map<std::string, Entry *> *c = new std::map<std::string, Entry *>();
     return *c;
 }
+// Compiles in flight.  A process that exits while NVRTC is still working on another thread crashes in
+// the library's teardown, so an exit handler — registered AFTER libnvrtc was loaded, hence run before
+// its destructors — waits for them (a second or two at most).
+int g_inFlight = 0;
+void waitForCompiles()
+{
+    for(;;)
+    {
+        {
+            std::lock_guard<std::mutex> g(cacheLock());
+            if(g_inFlight == 0)
+                return;
+        }
+        std::this_thread::sleep_for(std::chrono::milliseconds(5));
+    }
+}
 void compileEntry(Entry *e, std::string source)
 {
     const auto t0 = std::chrono::steady_clock::now();
@@ -311,6 +327,7 @@ void compileEntry(Entry *e, std::string source)
     e->log = log;
     e->cubin.swap(cubin);
     e->state = rc == 0 ? 1 : 2;
+    g_inFlight--;
 }
 } // namespace
 
@@ -318,6 +335,16 @@ const SpecKernels *specializeGet(const std::string &source, int device, int mode
 {
     Entry *e = nullptr;
     bool compileHere = false;
+    if(mode != SPEC_PEEK)
+    { // load NVRTC on this thread, then (once) register the exit handler: see waitForCompiles
+        std::lock_guard<std::mutex> g(g_lock);
+        static bool registered = false;
+        if(loadNvrtc() && !registered)
+        {
+            registered = true;
+            atexit(waitForCompiles);
+        }
+    }
     {
         std::lock_guard<std::mutex> g(cacheLock());
         auto it = cache().find(source);
@@ -327,6 +354,7 @@ const SpecKernels *specializeGet(const std::string &source, int device, int mode
         {
             e = new Entry();
             cache()[source] = e;
+            g_inFlight++;
             if(mode == SPEC_START)
                 std::thread(compileEntry, e, source).detach();
             else
