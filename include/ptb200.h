@@ -324,6 +324,20 @@ int ptb200_specialize_probe(const PtbSceneDesc *desc, int which /* 0: render tra
                             size_t *source_length, size_t *cubin_bytes);
 int ptb200_scene_specialized(PtbScene *scene, double *compile_ms, int *passes_specialized, int *passes_total);
 
+/* Tile wire text of the reference's TCP render farm, host only; sockets stay with the
+ * caller.  Server side (src/test.cpp:678-716): _request_parse reads the client's " x y size" line with
+ * the reference's validity checks; _encode writes every pixel of tile [x,x+size) x [y,y+size) of a
+ * width x height RGBA frame that has a value (alpha > 0) and is not flagged in sent[] (size*size bytes,
+ * updated; NULL = send all) as "P<x>,<y>=<r>,<g>,<b>\n" (printf %i / %g, RenderBlock::copyToSocket
+ * :372-391), then "E\n", then "F\n" when final != 0 (:715); *length = bytes written (without the NUL);
+ * out == NULL only measures.  Client side (NetRenderBlock::run, :596-630): _decode consumes such text
+ * into a size x size tile (rgb_tile: 3 floats per pixel, valid: 1 per pixel received), skipping 'S',
+ * 'E' and newlines, PTB_EINVAL on a pixel outside the tile or an unknown record; *finished = 1 at 'F';
+ * an incomplete last record is left unconsumed (*consumed = bytes used). */
+int ptb200_tile_request_parse(const char *line, int screen_width, int screen_height, int *x, int *y, int *size);
+int ptb200_tile_encode(const float *rgba, int width, int height, int x, int y, int size, uint8_t *sent, int final, char *out, size_t capacity, size_t *length);
+int ptb200_tile_decode(const char *text, size_t length, int x, int y, int size, float *rgb_tile, uint8_t *valid, int *finished, size_t *consumed);
+
 /* Draws n scatter directions (n x 3 floats, host) from the lobe sampler of the shading kernel for
  * one unit normal, un-normalised mirror vector and scatter coefficient (reference
  * include/path-trace.h:140-158); (0,0,0) marks a dropped vertex.  For statistical checks. */

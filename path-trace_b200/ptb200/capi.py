@@ -96,7 +96,7 @@ assert HIT_DTYPE.itemsize == 32 and SPAN_DTYPE.itemsize == 48
 ABI_SYMBOLS = [
     "ptb200_last_error", "ptb200_abi_version", "ptb200_device_count", "ptb200_trim", "ptb200_scene_create", "ptb200_scene_destroy", "ptb200_image_upload",
     "ptb200_intersect", "ptb200_intersect_device", "ptb200_texture_eval", "ptb200_render", "ptb200_render_adaptive", "ptb200_render_accumulate_device", "ptb200_resolve_device", "ptb200_display8_device", "ptb200_display8",
-    "ptb200_render_async", "ptb200_job_done", "ptb200_job_read", "ptb200_job_wait", "ptb200_job_destroy", "ptb200_sample_scatter", "ptb200_fp32_peak", "ptb200_specialize_probe", "ptb200_scene_specialized",
+    "ptb200_render_async", "ptb200_job_done", "ptb200_job_read", "ptb200_job_wait", "ptb200_job_destroy", "ptb200_sample_scatter", "ptb200_fp32_peak", "ptb200_specialize_probe", "ptb200_scene_specialized", "ptb200_tile_request_parse", "ptb200_tile_encode", "ptb200_tile_decode",
 ]
 
 _vp, _f, _i, _sz = C.c_void_p, C.c_float, C.c_int, C.c_size_t
@@ -202,6 +202,9 @@ def product():
         lib.ptb200_sample_scatter.argtypes = [_fp, _fp, _f, _sz, C.c_uint64, C.c_uint32, _vp]
         lib.ptb200_specialize_probe.argtypes = [C.POINTER(PtbSceneDesc), _i, C.c_char_p, _sz, C.POINTER(_sz), C.POINTER(_sz)]
         lib.ptb200_scene_specialized.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(_i), C.POINTER(_i)]
+        lib.ptb200_tile_request_parse.argtypes = [C.c_char_p, _i, _i, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i)]
+        lib.ptb200_tile_encode.argtypes = [_vp, _i, _i, _i, _i, _i, _vp, _i, C.c_char_p, _sz, C.POINTER(_sz)]
+        lib.ptb200_tile_decode.argtypes = [C.c_char_p, _sz, _i, _i, _i, _vp, _vp, C.POINTER(_i), C.POINTER(_sz)]
         lib.ptb200_fp32_peak.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double)]
         bind_builder(lib, "ptbh_")
         lib.ptbh_flatten.restype = _vp
