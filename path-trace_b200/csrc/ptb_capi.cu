@@ -525,6 +525,7 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
         return tag | (tag << 16);
     };
     std::vector<size_t> skipWord(nItems, 0); // SKIP word to patch when item i has been emitted
+    std::vector<size_t> leafWord(nItems, (size_t)-1); // header word of every transformed-sphere leaf
     size_t header = 0; // word that can still take operators
     bool sealed = true, freshLeaf = false;
     // the open cluster record: it takes the operators that follow its subtree, exactly those the
@@ -623,6 +624,7 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
                     c0 += (M[r][3] - (double)p.p[r]) * (M[r][3] - (double)p.p[r]);
                 out.push_back(make_uint4(FK_SPHERE_XF | FH_MISS_SHIFT, tagsOf(seq[i].prim), negR2, f2u((float)c0)));
                 header = out.size() - 1;
+                leafWord[i] = header;
                 for(int r = 0; r < 3; r++)
                     out.push_back(make_uint4(f2u((float)M[r][0]), f2u((float)M[r][1]), f2u((float)M[r][2]), f2u((float)(M[r][3] - (double)p.p[r]))));
             }
@@ -650,6 +652,50 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
                 allUnion = false;
         if(allUnion)
             out[w].x |= FH_UNION_TAIL;
+    }
+    { // Sphere runs: a complete Union-only subtree of 3..15 transformed spheres whose records are adjacent and
+      // which no operator follows directly (it is a left operand, or the root).  If no ray of a warp of CAMERA
+      // rays hits any of them, all the subtree does is push one empty list: the evaluator tests the run's
+      // discriminants in one loop with one vote and jumps over it (ptb_csg_fast.cuh, FH_RUN); otherwise it
+      // runs the leaves one by one as before.  The same leaf tests decide, so nothing changes in the results.
+        struct Sub
+        {
+            int first;
+            bool pure;
+        };
+        std::vector<Sub> stack, sub(seq.size());
+        for(size_t i = 0; i < seq.size(); i++)
+        {
+            if(seq[i].kind == PTB_OP_PUSH_PRIM)
+            {
+                const PtbPrim &p = d->prims[seq[i].prim];
+                stack.push_back(Sub{(int)i, p.type == PTB_PRIM_SPHERE && p.chain >= 0 && d->chains[p.chain].count > 0});
+            }
+            else
+            {
+                Sub b = stack.back();
+                stack.pop_back();
+                Sub &a = stack.back();
+                a.pure = a.pure && b.pure && seq[i].kind == PTB_OP_UNION;
+            }
+            sub[i] = stack.back();
+        }
+        int covered = (int)seq.size();
+        for(int i = (int)seq.size() - 1; i >= 0; i--)
+        {
+            if(!(i < covered && seq[i].kind != PTB_OP_PUSH_PRIM && sub[i].pure))
+                continue;
+            const int f = sub[i].first, n = (i - f) / 2 + 1;
+            covered = f; // maximal subtrees only
+            if(n < 3 || n > 15 || (i + 1 < (int)seq.size() && seq[i + 1].kind != PTB_OP_PUSH_PRIM))
+                continue;
+            bool adjacent = leafWord[f] != (size_t)-1 && !(out[leafWord[f]].x & FH_TAIL);
+            for(int k = f, leaf = 0; k <= i && adjacent; k++)
+                if(seq[k].kind == PTB_OP_PUSH_PRIM)
+                    adjacent = leafWord[k] == leafWord[f] + 4u * (size_t)leaf++;
+            if(adjacent)
+                out[leafWord[f]].x |= FH_RUN | ((uint32_t)n << 12);
+        }
     }
     for(size_t w = 0; w < out.size();)
     {
@@ -1348,6 +1394,12 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
     pass.flags = p->flags;
     uint64_t launches = 0;
     int specPasses = 0;
+    // Queued (bounce) rays are incoherent: nearly every leaf is hit by some lane of the warp, the
+    // specialised block then calls its out-of-line half and ends up behind the interpreter's single inline
+    // site (C5: 211-231 ms against 207-222).  They stay interpreted unless the caller forces
+    // specialisation (the parity tests do) or PTB_SPEC_BOUNCE=1.
+    static const bool specBounceEnv = getenv("PTB_SPEC_BOUNCE") && atoi(getenv("PTB_SPEC_BOUNCE")) != 0;
+    const bool specBounce = specBounceEnv || (p->flags & PTB_FLAG_SPECIALIZE) != 0;
     for(int i = 0; i < nPasses; i++)
     {
         unsigned *c = (unsigned *)sx.counters.p + (size_t)i * (stages + 1);
@@ -1375,7 +1427,7 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
             CU(cudaEventRecord(ev[2], stream));
         for(int b = 1; b <= p->max_depth; b++)
         {
-            if(sp.k)
+            if(sp.k && specBounce)
             {
                 RayQueue qin = q[(b - 1) & 1];
                 const unsigned *cin = c + (b - 1);

@@ -56,6 +56,7 @@ enum
     FH_MISS_SHIFT = 1 << 6,
     FH_TAIL = 1 << 7,
     FH_UNION_TAIL = 1 << 30, // every operator of the tail is a Union (and the action is not Intersection)
+    FH_RUN = 1 << 30,        // SPHERE_XF WITHOUT a tail: first of a run of (x >> 12) & 15 adjacent leaves forming a whole Union subtree
     FH_PAIR = 1u << 31       // SPHERE_XF without tail directly followed by another SPHERE_XF leaf
 };
 enum
@@ -495,6 +496,31 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
             ltags[r] = h.y; // (the rest is set by the branch that sets hit[r]; two[r], ut0[r], utags[r] by planes only)
         if(h.x & FK_SPHERE_XF)
         {
+            if(O0 && (h.x & (FH_RUN | FH_TAIL)) == FH_RUN)
+            { // camera rays: the whole Union subtree of spheres in one loop and one vote (see compileFastProgram).
+              // ncu, C4: a leaf costs ~49 instructions one by one, 17 of them arithmetic; ~26 here.
+                const uint32_t n = (h.x >> 12) & 15u;
+                bool any = false;
+                for(uint32_t k = 0; k < n; k++)
+                {
+                    const uint4 g = PTB_PROG(4u * k), v0 = PTB_PROG(4u * k + 1u), v1 = PTB_PROG(4u * k + 2u), v2 = PTB_PROG(4u * k + 3u);
+#pragma unroll
+                    for(int r = 0; r < R; r++)
+                    {
+                        float ra, rb, re;
+                        xfDisc<O0>(g, v0, v1, v2, o[r], d[r], ra, rb, re);
+                        any = any || re > PTB_EPS;
+                    }
+                }
+                if(!__any_sync(0xFFFFFFFFu, any))
+                { // every leaf missed: the subtree is one empty list
+#pragma unroll
+                    for(int r = 0; r < R; r++)
+                        st[r].bits <<= 1;
+                    PTB_ADVANCE(4u * n);
+                    continue;
+                }
+            }
             const uint4 u0 = PTB_PROG(1), u1 = PTB_PROG(2), u2 = PTB_PROG(3);
             float a[R], b[R], e[R];
             if(h.x & FH_PAIR)

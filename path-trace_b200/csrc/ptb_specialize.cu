@@ -225,11 +225,14 @@ std::string specializeSource(const std::vector<uint4> &prog, int which)
 
 int specializeCompile(const std::string &source, std::vector<char> &cubin, std::string &log)
 {
-    std::lock_guard<std::mutex> g(g_lock);
-    if(!loadNvrtc())
-    {
-        log = g_libs.why;
-        return -1;
+    { // the lock covers loading the library only: a render thread that polls for the kernels while another
+      // thread compiles must not wait for the compile (NVRTC compiles separate programs concurrently)
+        std::lock_guard<std::mutex> g(g_lock);
+        if(!loadNvrtc())
+        {
+            log = g_libs.why;
+            return -1;
+        }
     }
     void *prog = nullptr;
     int rc = g_libs.nvrtcCreateProgram(&prog, source.c_str(), "ptb_scene.cu", kEmbeddedCount, kEmbeddedSources, kEmbeddedNames);
