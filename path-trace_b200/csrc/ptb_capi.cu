@@ -1592,7 +1592,8 @@ extern "C" int ptb200_render_adaptive(PtbScene *s, const PtbRenderParams *p, con
     auto align = [](size_t n) { return (n + 255) & ~(size_t)255; };
     const size_t oValue = 0, oInterp = oValue + align(nLattice * 16), oReq = oInterp + align(nLattice * 16), oSqA = oReq + align(nLattice * 4),
                  oSqB = oSqA + align(maxSquares * 4), oList = oSqB + align(maxSquares * 4), oCnt = oList + align(nLattice * 4), oOut = oCnt + 256,
-                 oSrc = oOut + align(nPix * 16), total = oSrc + align(nPix);
+                 oSrc = oOut + align(nPix * 16), oAlt = oSrc + align(nPix), oTemp = oAlt + align(nLattice * 4),
+                 sortBytes = align(adaptiveSortList(nullptr, nullptr, (unsigned)nLattice, nullptr, 0, nullptr)), total = oTemp + sortBytes;
     CU(sx.adaptive.ensure(total));
     CU(sx.accum.ensure(nLattice * 16));
     char *base = (char *)sx.adaptive.p;
@@ -1658,6 +1659,8 @@ extern "C" int ptb200_render_adaptive(PtbScene *s, const PtbRenderParams *p, con
         as.squares_interpolated += c[2];
         as.pixels_interpolated += c[3];
         nSquares = c[0], nList = c[1], cur ^= 1;
+        adaptiveSortList(list, (uint32_t *)(base + oAlt), nList, base + oTemp, sortBytes, nullptr); // back into image order: coherent camera rays
+        CU(cudaGetLastError());
         if(int rc = traceList(nList))
             return rc;
     }

@@ -10,6 +10,8 @@
 // into shared memory once per CTA and read warp-uniformly; span lists sit in a bank-conflict
 // free [slot][thread] shared-memory pool; queue records are four float4 SoA streams written
 // through __ballot_sync/__popc warp-aggregated compaction so every store is coalesced.
+#include <cub/device/device_radix_sort.cuh>
+
 #include "ptb_launch.h"
 #include "ptb_trace.cuh"
 #include "ptb_shade.cuh"
@@ -461,6 +463,19 @@ void launchAdaptiveDecide(const AdaptiveLevel &lv, cudaStream_t stream)
         return;
     int blocks = (int)((lv.nSquares + 127u) / 128u);
     adaptiveDecideKernel<<<blocks > 148 * 16 ? 148 * 16 : blocks, 128, 0, stream>>>(lv);
+}
+
+size_t adaptiveSortList(uint32_t *list, uint32_t *alt, unsigned n, void *temp, size_t tempBytes, cudaStream_t stream)
+{
+    size_t need = 0;
+    cub::DeviceRadixSort::SortKeys(nullptr, need, list, alt, (int)n, 0, 32, stream);
+    if(tempBytes == 0 || n < 2u)
+        return need;
+    if(tempBytes < need)
+        return 0;
+    cub::DeviceRadixSort::SortKeys(temp, need, list, alt, (int)n, 0, 32, stream);
+    cudaMemcpyAsync(list, alt, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream);
+    return need;
 }
 
 __global__ void adaptiveResolveListKernel(const float4 *__restrict__ accum, float4 *__restrict__ value, const uint32_t *__restrict__ pixelList, unsigned n, int pitch)

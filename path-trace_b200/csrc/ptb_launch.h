@@ -114,6 +114,9 @@ struct AdaptiveLevel
     unsigned *counters;      // [0] = child squares, [1] = pixel list length, [2] = squares interpolated, [3] = pixels interpolated
 };
 void launchAdaptiveDecide(const AdaptiveLevel &lv, cudaStream_t stream);
+// Sorts a pixel list by (y, x): the decide kernel appends in atomic order, and camera rays of scattered
+// pixels are as incoherent as bounce rays (2x slower to trace).  tempBytes = 0: returns the scratch size.
+size_t adaptiveSortList(uint32_t *list, uint32_t *alt, unsigned n, void *temp, size_t tempBytes, cudaStream_t stream);
 // value[p] = (accum[p].rgb / accum[p].a, 1) for every listed lattice point
 void launchAdaptiveResolveList(const float4 *accum, float4 *value, const uint32_t *pixelList, unsigned n, int pitch, cudaStream_t stream);
 // rgba (width x height) = interpolated pixel where there is one, else the traced one; source: 1 traced, 2 interpolated

@@ -104,7 +104,7 @@ class DeviceScene:
         check(capi.product().ptb200_render(self.handle, C.byref(params), out.ctypes.data, C.byref(stats)))
         return out, stats
 
-    def render_adaptive(self, params, block_size=32, max_sample_size=None, min_color_delta=0.003):
+    def render_adaptive(self, params, block_size=32, max_sample_size=None, min_color_delta=0.003, want_lattice=True):
         """ptb200_render_adaptive: the reference's pixel-skipping quadtree (src/test.cpp:423-499).
         Defaults are the reference's constants (src/test.cpp:38,50).  Returns image, source map
         (1 traced, 2 interpolated), traced lattice, PtbStats, PtbAdaptiveStats."""
@@ -117,7 +117,7 @@ class DeviceScene:
         bs = max(1, block_size)  # bad sizes are rejected by the library, not here
         lattice = np.zeros((-(-params.height // bs) * bs + 1, -(-params.width // bs) * bs + 1, 4), np.float32)
         stats, astats = PtbStats(), capi.PtbAdaptiveStats()
-        check(capi.product().ptb200_render_adaptive(self.handle, C.byref(params), C.byref(ap), out.ctypes.data, source.ctypes.data, lattice.ctypes.data, C.byref(stats), C.byref(astats)))
+        check(capi.product().ptb200_render_adaptive(self.handle, C.byref(params), C.byref(ap), out.ctypes.data, source.ctypes.data, lattice.ctypes.data if want_lattice else None, C.byref(stats), C.byref(astats)))
         return out, source, lattice, stats, astats
 
     def specialized(self):
