@@ -31,6 +31,22 @@ def test_generated_source_compiles_for_sm100a():
     assert source.count("xfDisc<O0>") >= 48 and source.count("planeFold<O0>") >= 22
 
 
+def test_sphere_runs_are_marked_in_the_compiled_stream():
+    """compileFastProgram flags the first leaf of every complete Union subtree of transformed spheres
+    (FH_RUN, bit 30 of a header without tail, run length in bits 12-15): the eight groups of six
+    spheres of config 4; config 5 (untransformed spheres in a mixed tree) has none."""
+    import re
+    b = product_builder()
+
+    def run_headers(world):
+        source, _ = device.specialize_probe(device.Flat(world), 0, compile=False)
+        heads = [int(h, 16) for h in re.findall(r"xfDisc<O0>\(make_uint4\((0x[0-9a-f]{8})u", source)]
+        return [(h >> 12) & 15 for h in heads if (h & 0x40000080) == 0x40000000]
+
+    assert run_headers(scenes.config4(b)) == [6] * 8
+    assert run_headers(scenes.config5(b)) == []
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("case", ["c3", "c4_camera", "c5", "fuzz11", "fuzz12", "fuzz13"])
 def test_specialised_ray_batches_equal_the_interpreter_bitwise(case):
