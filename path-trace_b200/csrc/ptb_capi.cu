@@ -1071,6 +1071,8 @@ static int chooseSpec(PtbScene *s, uint32_t flags, double work, int which, SpecC
     CsgConfig &cfg = sp.cfg;
     cfg.threads = PTB_FAST_THREADS, cfg.fast = 1, cfg.stageProgram = 0;
     cfg.cap = std::min(dev.poolBound, 12);
+    if(const char *e = getenv("PTB200_POOL_CAP")) // tests: force lists into the global overflow area
+        cfg.cap = std::max(2, std::min(dev.poolBound, atoi(e)));
     cfg.smemBytes = fastSharedBytes(dev, cfg.cap, false, 1);
     if(cfg.smemBytes > s->smemOptin)
         return PTB_OK;

@@ -78,6 +78,23 @@ def test_specialised_ray_batches_equal_the_interpreter_bitwise(case):
 
 
 @pytest.mark.gpu
+def test_specialised_kernels_with_span_pool_overflow(monkeypatch):
+    """A two-slot shared-memory pool: span lists of the specialised kernels spill to the global overflow
+    area (SpecShared.ovf) and still equal the interpreter's with its default pool."""
+    b = product_builder()
+    scene = device.DeviceScene(device.Flat(gc.render_scene(b, "c4")))
+    rs = np.random.RandomState(9)
+    n = 20000
+    o = rs.uniform(-3, 3, (n, 3)).astype(np.float32) + np.array([0, 0, -9.0], np.float32)
+    d = rs.normal(size=(n, 3)).astype(np.float32)
+    h0, s0 = scene.intersect(o, d, 12, INTERP)
+    monkeypatch.setenv("PTB200_POOL_CAP", "2")
+    h1, s1 = scene.intersect(o, d, 12, SPEC)
+    assert h0.tobytes() == h1.tobytes() and s0.tobytes() == s1.tobytes()
+    assert (h0["n_spans"] > 2).any()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("name", ["c2", "c4", "c5"])
 def test_specialised_render_equals_the_interpreter(name):
     b = product_builder()
