@@ -130,6 +130,8 @@ std::string label(size_t w) { return "W" + std::to_string(w); }
 std::string specializeSource(const std::vector<uint4> &prog, int which)
 {
     std::string s;
+    if(const char *e = getenv("PTB_SPEC_MIN_CTAS")) // experiment: resident CTAs per SM the trace kernels are compiled for; default 8 = 64 registers (C5 camera-ray trace: 6 -> 288 ms, 7 -> 272, 8 -> 267, 10 -> 306 with spills, 12 -> 318)
+        s += "#define PTB_TRACE_MIN_CTAS " + std::to_string(atoi(e)) + "\n";
     s += "#include \"ptb200.h\"\n#include \"ptb_csg_spec.cuh\"\nnamespace ptb\n{\n";
     s += "template <bool O0>\n__device__ __forceinline__ void evalSpec(const FastCtx &c, const V3 o, const V3 d, int &topOut)\n{\n";
     s += "    FastState st;\n    st.bits = 0u, st.top = 0, st.sp = c.stk;\n";
