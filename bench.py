@@ -6,13 +6,20 @@
 
 One "step" = one whole frame of the workload (default: config 5, 3840x2160 at 1024 camera samples per
 pixel).  With N > 1 (launched by torch.distributed.run, one rank per GPU) the 1024 samples are sharded
-across ranks (rank g renders global samples g, g+N, ...), the accumulation buffers are summed to rank 0
-with one NCCL reduce inside the timed step and rank 0 resolves the image: strong scaling.
+across ranks (rank g renders global samples g, g+N, ...) by ptb200_render_multi: NCCL reduce-scatter of
+row blocks, every rank resolves and downloads its own rows — strong scaling.
 
-Prints ONE JSON line (rank 0).  `value` = Mrays/s with the scene resident in HBM, device-timed with
-CUDA events; `e2e` = the same through the host-buffer C-ABI calls (scene upload + render + image
-download inside the timed region); `roofline` = the wavefront stage kernels against the measured FP32
-issue peak; `cpu_baseline` = the unmodified reference (oracle/_ref) on this box's host cores, bounded.
+Prints ONE JSON line (rank 0):
+  value        Mrays/s with the scene resident in HBM, device-timed with CUDA events over K steps
+  e2e          the same through the host-buffer C-ABI calls (scene upload + render + image download
+               inside the timed region), over the same K steps
+  roofline     the kernel with the largest share of the step, plus roofline.kernels[]: one entry per
+               kernel class, each against ITS bound — trace kernels against the measured FP32 issue peak
+               with TRACE-ONLY flops, shade kernels against the measured HBM copy peak with a bytes
+               model — and the ncu counters of the same kernels (profiles/ncu_kernels.json)
+  secondary    c4 (the 4K deep-CSG scene the north-star FP32 target is stated on, >= 5 steps) and c3
+               (2^26 device-resident rays through ptb200_intersect_device, fast policy), N = 1 only
+  cpu_baseline the unmodified reference (oracle/_ref) on this box's host cores, bounded
 """
 import argparse
 import ctypes as C
@@ -36,19 +43,31 @@ WORKLOADS = {
     "c2": (1920, 1080, 256, "config 2: diffuse sphere on a plane under a constant sky, 1920x1080, 256 spp"),
     "c1": (1920, 1080, 1024, "config 1: makeWorld() default scene (synthetic env in place of the missing Serpentine_Valley_3k.hdr), 1920x1080"),
 }
+C3_DESC = "config 3: 2^26 random rays vs the 16-primitive Union/Difference tree (12 spheres, 4 cutter planes), device-resident float4 rays"
+MAX_DEPTH = 16
+SHADE_FLOPS = 6 + 31 + 22 + 60 + 12 + 27  # hit point, refractStrength, reflect, scatter sample, accumulate, normal
+CAMERA_FLOPS = 14
+
+
+def workload_config(name, spp=None):
+    """The `config` object of the JSON line: identical for the `ours` and `reference` arms."""
+    width, height, wspp, desc = WORKLOADS[name]
+    return {"workload": desc, "width": width, "height": height, "spp": spp or wspp, "max_depth": MAX_DEPTH,
+            "l2": "accumulation buffer (133 MB at 4K) is rewritten and the ray queues (GBs) stream through HBM every step: working set >> 126 MB L2"}
 
 
 def build_world(b, name):
     from ptb200 import scenes
-    return {"c5": scenes.config5, "c4": scenes.config4, "c2": scenes.config2, "c1": scenes.config1}[name](b)
+    return {"c5": scenes.config5, "c4": scenes.config4, "c3": scenes.config3, "c2": scenes.config2, "c1": scenes.config1}[name](b)
 
 
-def flops_per_ray(desc):
-    """Frozen algorithmic work model (DESIGN.md 'work model'): every f32
-    add/mul/cmp/div/sqrt counts 1, an FMA-able pair 2.  Sphere test 22 (the miss cost — normals are
-    only computed for the one boundary hit), plane 14, each TransformedObject level 33 per leaf, 4 per
-    merge-loop iteration (3 iterations per operator), 4 per scanned span (2 spans), and a shaded vertex
-    (hit point 6, refractStrength 31, reflect 22, scatter sample 60, accumulate 12, normal 27)."""
+def trace_flops_per_ray(desc):
+    """Frozen algorithmic work model of the TRACE side (DESIGN.md 'work model'): every
+    f32 add/mul/cmp/div/sqrt counts 1, an FMA-able pair 2.  Sphere test 22 (the miss cost — normals are
+    only computed for the one boundary hit, in the shade kernel), plane 14, each TransformedObject level
+    33 per leaf, 4 per merge-loop iteration (3 iterations per operator), 4 per scanned span (2 spans).
+    The camera ray (14) is added for primary rays; the shaded vertex (158) belongs to the SHADE kernels
+    and is never credited to a trace kernel."""
     total = 0.0
     for i in range(desc.n_prims):
         p = desc.prims[i]
@@ -57,7 +76,6 @@ def flops_per_ray(desc):
             total += 33 * desc.chains[p.chain].count
     n_ops = desc.n_ops - desc.n_prims
     total += 4 * 3 * n_ops + 4 * 2
-    total += 6 + 31 + 22 + 60 + 12 + 27
     return total
 
 
@@ -91,6 +109,7 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "power_w_max": max(float(r[2]) for r in self.rows), "reasons": reasons, "samples": len(self.rows)}
 
 
+# ---- the reference's CPU implementation on the host cores ------------------------------------------
 def cpu_reference_rate(name, seconds, width, height):
     """The reference's own CPU renderer (unmodified sources in oracle/_ref, else the oracle port) on
     all host cores: the 192x108-style lattice of the workload's image plane, rows until `seconds`."""
@@ -105,14 +124,15 @@ def cpu_reference_rate(name, seconds, width, height):
         lib = common.ref(fast)
         rb = common.ref_builder(fast)
         world = build_world(rb, name)
-        _, info = common.ref_render_mt(lib, world, width, height, step // 2, step // 2, step, nx, ny, 1, 16, 99, cores, seconds)
+        _, info = common.ref_render_mt(lib, world, width, height, step // 2, step // 2, step, nx, ny, 1, MAX_DEPTH, 99, cores, seconds)
         kind = "reference"
-        build = "oracle/_ref/libptref_fast.so (-O3 -march=x86-64-v3)" if fast else "oracle/_ref/libptref.so (-O3, no FMA)"
+        build = ("oracle/_ref/libptref_fast.so (-O3 -march=x86-64-v3" if fast else "oracle/_ref/libptref.so (-O3, no FMA") + \
+            "; -DNDEBUG, which the reference's Release target does not set: its assert(count <= 1000), include/path-trace.h:148, aborts on config 4 — oracle/Makefile)"
     else:
         from ptb200 import device
         from ptb200.builder import product_builder
         flat = device.Flat(build_world(product_builder(), name))
-        _, info = common.orc_render_mt(flat, width, height, step // 2, step // 2, step, nx, ny, 1, 16, 99, cores, seconds)
+        _, info = common.orc_render_mt(flat, width, height, step // 2, step // 2, step, nx, ny, 1, MAX_DEPTH, 99, cores, seconds)
         build = "oracle/libptoracle.so (CPU restatement)"
     secs = max(info["seconds"], 1e-9)
     return {
@@ -121,6 +141,39 @@ def cpu_reference_rate(name, seconds, width, height):
         "sample": "%s, every %dth pixel of the %dx%d image plane, 1 camera sample/px (each = the reference's ~10^4-ray branching estimate), %d px in %.1f s; %s"
                   % (name, step, width, height, info["pixels"], secs, build),
     }
+
+
+def cpu_reference_c3(n_sample, origins, dirs):
+    """The reference's SpanIterator tree (unmodified sources) on a bounded sample of the C3 batch, all
+    host cores (one chunk per thread; ctypes releases the GIL).  Returns Mrays/s."""
+    import common
+    from concurrent.futures import ThreadPoolExecutor
+    cores = os.cpu_count() or 1
+    o = np.ascontiguousarray(origins[:n_sample, :3], np.float32)
+    d = np.ascontiguousarray(dirs[:n_sample, :3], np.float32)
+    if common.have_ref():
+        rb = common.ref_builder(False)
+        world = build_world(rb, "c3")
+        kind, what = "reference", "oracle/_ref/libptref.so Object::makeSpanIterator + init/next over the whole root list"
+
+        def run(k):
+            lo, hi = k * n_sample // cores, (k + 1) * n_sample // cores
+            rb.trace_spans(world, o[lo:hi], d[lo:hi], 12)
+    else:
+        from ptb200 import device
+        from ptb200.builder import product_builder
+        flat = device.Flat(build_world(product_builder(), "c3"))
+        kind, what = "port", "oracle/libptoracle.so orc_intersect"
+
+        def run(k):
+            lo, hi = k * n_sample // cores, (k + 1) * n_sample // cores
+            common.orc_intersect(flat, o[lo:hi], d[lo:hi], 12)
+    run(0)  # warm
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(cores) as ex:
+        list(ex.map(run, range(cores)))
+    secs = time.perf_counter() - t0
+    return {"value": n_sample / secs / 1e6, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": "first %d rays of the same batch in %.2f s; %s" % (n_sample, secs, what)}
 
 
 def run_reference(args):
@@ -133,7 +186,7 @@ def run_reference(args):
     for _ in range(args.warmup):
         cpu_reference_rate(args.workload, min(per_step, 1.0), width, height)
     t0 = time.time()
-    rays = pixels = secs = 0.0
+    rays = pixels = 0.0
     last = None
     for _ in range(args.steps):
         last = cpu_reference_rate(args.workload, per_step, width, height)
@@ -146,9 +199,177 @@ def run_reference(args):
     print(json.dumps({
         "impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": wall / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "sample": base["sample"]}, "mpaths_per_s": pixels / args.steps / 1e6, "cpu_baseline": base,
+        "config": workload_config(args.workload, args.spp or None), "mpaths_per_s": pixels / args.steps / 1e6, "cpu_baseline": base,
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
     }))
+
+
+# ---- our arm ------------------------------------------------------------------------------------------
+def load_json(*path):
+    try:
+        return json.load(open(os.path.join(ROOT, *path)))
+    except Exception:
+        return {}
+
+
+def kernel_rooflines(name, desc, st, n_pix, passes, fp32_peak_tflops, hbm_peak_gbs, spec_all):
+    """One roofline entry per kernel class of the wavefront, from the CUDA-event times the library
+    took around every launch of the instrumented step (PtbStats).  Trace kernels: FP32 issue bound,
+    trace-only flops.  Shade kernels: HBM bound, algorithmic bytes:
+      primary shade  8 B hit record per path + 64 B per survivor written + the accumulation buffer read
+                     and written once per pass (32 B per pixel per pass)
+      bounce shade   8 B hit + 64 B queue record per ray read + 64 B per survivor written + 32 B
+                     (float4 atomic: read + write) per path that ends there
+    ncu counters of the same kernels (DRAM bytes per launch = `traffic`, FMA-pipe and issue-active
+    percentages, instructions per ray) come from profiles/ncu_kernels.json, captured with
+    `ncu --set full` on the same workload."""
+    ncu = load_json("profiles", "ncu_kernels.json").get(name, {})
+    fpr = trace_flops_per_ray(desc)
+    total_ms = max(st.ms_trace_primary + st.ms_shade_primary + st.ms_trace_bounce + st.ms_shade_bounce, 1e-9)
+    survivors_bounce = max(int(st.rays_bounce) - int(st.rays_first_bounce), 0)
+    finished_bounce = max(int(st.rays_bounce) - survivors_bounce, 0)
+    launches_per_class = max(1, passes)
+    spec = "ptbSpecTracePrimary (scene-specialised, NVRTC)" if spec_all else "tracePrimaryKernel (interpreter)"
+    rows = [
+        ("trace_primary", spec, "fp32", st.ms_trace_primary, st.rays_primary, st.rays_primary * (fpr + CAMERA_FLOPS), "%d flop/ray (model %d + camera %d)" % (fpr + CAMERA_FLOPS, fpr, CAMERA_FLOPS)),
+        ("shade_primary", "shadeKernel<primary>", "hbm", st.ms_shade_primary, st.rays_primary,
+         8.0 * st.rays_primary + 64.0 * st.rays_first_bounce + 32.0 * n_pix * passes, "8 B/path + 64 B/survivor + 32 B/pixel/pass"),
+        ("trace_bounce", "traceQueueKernel (interpreter)", "fp32", st.ms_trace_bounce, st.rays_bounce, st.rays_bounce * fpr, "%d flop/ray" % fpr),
+        ("shade_bounce", "shadeKernel<bounce>", "hbm", st.ms_shade_bounce, st.rays_bounce,
+         72.0 * st.rays_bounce + 64.0 * survivors_bounce + 32.0 * finished_bounce, "72 B/ray + 64 B/survivor + 32 B/finished path"),
+    ]
+    out = []
+    for key, kernel, bound, ms, units, work, model in rows:
+        if bound == "fp32":
+            achieved, peak, unit = (work / (ms * 1e-3) / 1e12 if ms > 0 else 0.0), fp32_peak_tflops, "TFLOP/s"
+        else:
+            achieved, peak, unit = (work / (ms * 1e-3) / 1e9 if ms > 0 else 0.0), hbm_peak_gbs, "GB/s"
+        e = {"class": key, "kernel": kernel, "bound": bound, "ms": ms, "share": ms / total_ms, "launches": launches_per_class if "primary" in key else launches_per_class * MAX_DEPTH,
+             "units": int(units), "unit_rate": (units / (ms * 1e-3) / 1e6 if ms > 0 else 0.0), "unit_rate_unit": "Mrays/s", "achieved": achieved, "peak": peak, "unit": unit,
+             "frac": achieved / peak if peak else None, "model": model, "traffic": None}
+        k = ncu.get(key)
+        if k:
+            e["traffic"] = k.get("dram_bytes_per_launch")
+            e["ncu"] = k
+        out.append(e)
+    return out
+
+
+def run_render(scene, flat, name, width, height, spp, steps, warmup, samples_per_pass, torch, stream, accum, rgba, step_fn=None):
+    """Device-timed render of one workload on the CURRENT rank (scene resident in HBM): returns
+    (ms_per_step of this rank, PtbStats of one extra instrumented step)."""
+    from ptb200 import device
+
+    def step(want_stats):
+        accum.zero_()  # 133 MB write at 4K (> L2): also evicts the previous step's lines
+        st = scene.render_accumulate(device.default_params(width, height, spp, seed=0xB200, samples_per_pass=samples_per_pass), accum, stream, want_stats)
+        device.resolve(accum, rgba, stream)
+        return st
+
+    step = step_fn or step
+    for _ in range(warmup):
+        step(False)
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(steps):
+        step(False)
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1) / steps
+    st = step(True)
+    torch.cuda.synchronize()
+    return ms, st
+
+
+def c3_rays(torch, n, seed):
+    """The ray distribution of scenes.config3_rays, generated on the device."""
+    g = torch.Generator(device="cuda")
+    g.manual_seed(seed)
+
+    def ball(radius):
+        v = torch.randn((n, 3), device="cuda", generator=g)
+        v /= v.norm(dim=1, keepdim=True)
+        v *= radius * torch.rand((n, 1), device="cuda", generator=g) ** (1.0 / 3.0)
+        return v
+
+    o = ball(4.0)
+    d = ball(1.0)
+    norm = d.norm(dim=1, keepdim=True)
+    d = torch.where(norm < 1e-3, torch.tensor([0.0, 0.0, 1.0], device="cuda"), d)
+    unit = d / d.norm(dim=1, keepdim=True)
+    cls = (torch.arange(n, device="cuda") % 4).unsqueeze(1)
+    d = torch.where(cls == 2, unit, d)
+    d = torch.where(cls == 3, unit * 2400.0, d)
+    o4 = torch.zeros((n, 4), device="cuda")
+    d4 = torch.zeros((n, 4), device="cuda")
+    o4[:, :3] = o
+    d4[:, :3] = d
+    return o4, d4
+
+
+def run_c3(torch, steps, fp32_peak_tflops, hbm_peak_gbs, want_cpu):
+    """BASELINE config 3: Mrays/s of the 2^26-ray batch through ptb200_intersect_device (fast policy,
+    what the renderer runs), rays and hit records resident in HBM (2 GiB in, 2 GiB out per launch:
+    >> L2).  Also: agreement with the exact policy over the whole batch, the float64 grazing analysis
+    (tests/grazing.py) on every 64th ray, and the reference's CPU rays/s on a sample of the same batch."""
+    from ptb200 import capi, device
+    from ptb200.builder import product_builder
+    n = 1 << int(os.environ.get("PTB200_C3_LOG2", "26"))
+    flat = device.Flat(build_world(product_builder(), "c3"))
+    scene = device.DeviceScene(flat)
+    o4, d4 = c3_rays(torch, n, 0xB200 + 31)
+    hits = torch.zeros((n, 8), dtype=torch.int32, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    for _ in range(3):  # warm-up (also lets the background NVRTC compile of the scene-specialised kernel finish)
+        scene.intersect_device(o4, d4, hits, 0, stream)
+        torch.cuda.synchronize()
+        time.sleep(0.5)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    ev[0].record()
+    for k in range(steps):
+        scene.intersect_device(o4, d4, hits, 0, stream)
+        ev[k + 1].record()
+    torch.cuda.synchronize()
+    ms = ev[0].elapsed_time(ev[steps]) / steps
+    fast = hits.clone()
+    exact = torch.zeros_like(hits)
+    scene.intersect_device(o4, d4, exact, capi.PTB_FLAG_EXACT, stream)
+    torch.cuda.synchronize()
+    # PtbHit as 8 words: t, normal[3], kind, prim, material, n_spans
+    same = (fast[:, 4] == exact[:, 4]) & (fast[:, 5] == exact[:, 5]) & (fast[:, 7] == exact[:, 7])
+    hit = same & (exact[:, 4] > 0)
+    tf, te = fast[:, 0].view(torch.float32)[hit], exact[:, 0].view(torch.float32)[hit]
+    rel = ((tf - te).abs() / te.abs())
+    sub = slice(0, n, 64)
+    flagged = None
+    try:
+        from grazing import flag_grazing
+        topo, _ = flag_grazing(flat.desc, o4[sub, :3].cpu().numpy(), d4[sub, :3].cpu().numpy())
+        sub_same = same[sub].cpu().numpy()
+        flagged = {"fraction": float(topo.mean()), "rays_checked": int(topo.size), "unflagged_rays_that_differ_from_exact": int((~sub_same & ~topo).sum())}
+    except Exception as e:  # the analysis is reporting only
+        flagged = {"error": repr(e)}
+    fpr = trace_flops_per_ray(flat.desc)
+    achieved = n * fpr / (ms * 1e-3) / 1e12
+    ncu = load_json("profiles", "ncu_kernels.json").get("c3", {}).get("intersect")
+    out = {
+        "workload": C3_DESC, "metric": "Mrays/s", "value": n / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "rays": n, "steps": steps, "ms_per_step": ms,
+        "policy": "fast (FMA, folded geometry, MUFU rcp/sqrt); 32 B ray in, 32 B PtbHit out",
+        "hit_fraction": float((exact[:, 4] > 0).float().mean().item()),
+        "vs_exact_policy": {"same_kind_prim_nspans": float(same.float().mean().item()), "t_rel_err_p99": float(torch.quantile(rel[:: max(1, rel.numel() // (1 << 22))], 0.99).item()) if rel.numel() else None,
+                            "t_rel_err_le_1e-5": float((rel <= 1e-5).float().mean().item()) if rel.numel() else None},
+        "flagged_grazing": flagged,
+        "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak_tflops, "unit": "TFLOP/s", "frac": achieved / fp32_peak_tflops if fp32_peak_tflops else None,
+                     "model": "%d flop/ray" % fpr, "traffic": ncu.get("dram_bytes_per_launch") if ncu else None, "ncu": ncu,
+                     "hbm": {"achieved": n * 64.0 / (ms * 1e-3) / 1e9, "peak": hbm_peak_gbs, "unit": "GB/s", "frac": n * 64.0 / (ms * 1e-3) / 1e9 / hbm_peak_gbs}},
+        "specialized": scene.specialized()[0],
+    }
+    if want_cpu:
+        ns = 1 << 21
+        out["cpu_baseline"] = cpu_reference_c3(ns, o4[:ns].cpu().numpy(), d4[:ns].cpu().numpy())
+    scene.close()
+    return out
 
 
 def run_ours(args):
@@ -172,8 +393,6 @@ def run_ours(args):
     width, height, spp, desc = WORKLOADS[args.workload]
     if args.spp:
         spp = args.spp
-    if spp % world_size:
-        raise SystemExit("spp must be divisible by the number of GPUs")
     lib = capi.product()
     flat = device.Flat(build_world(product_builder(), args.workload))
     scene = device.DeviceScene(flat)
@@ -181,17 +400,24 @@ def run_ours(args):
     accum = torch.zeros((height, width, 4), device="cuda")
     rgba = torch.empty_like(accum)
     host_image = torch.empty((height, width, 4), pin_memory=True)
-    params = device.default_params(width, height, spp // world_size, seed=0xB200, sample_offset=rank, sample_stride=world_size, samples_per_pass=args.samples_per_pass)
+    host_np = host_image.numpy()
+    n_pix = width * height
 
     from ptb200 import multi
+    comm = multi.Communicator(dist) if world_size > 1 else None
 
     def make_params(**kw):
         return device.default_params(width, height, seed=0xB200, samples_per_pass=args.samples_per_pass, **kw)
 
     def step(want_stats):
-        accum.zero_()  # 132 MB write (> L2): also evicts the previous step's lines
-        return multi.render_sharded(lambda p, a: scene.render_accumulate(p, a, stream, want_stats), lambda a, o: device.resolve(a, o, stream),
-                                    make_params, spp, accum, rgba, dist if world_size > 1 else None)
+        if comm is None:
+            accum.zero_()  # 133 MB write (> L2): also evicts the previous step's lines
+            st = scene.render_accumulate(make_params(spp=spp), accum, stream, want_stats)
+            device.resolve(accum, rgba, stream)
+            return st
+        # N ranks: every rank renders its sample shard, NCCL reduce-scatter of row blocks inside the library,
+        # every rank resolves its own rows (device-resident output: rgba rows [r0, r1) of this rank)
+        return comm.render(scene, make_params(spp=spp), rgba, None, want_stats, stream)
 
     def barrier():
         if world_size > 1:
@@ -215,7 +441,7 @@ def run_ours(args):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_per_step = ms.item() / args.steps
 
-    # one extra instrumented step for ray counts and per-stage device times (CUDA events inside the library)
+    # one extra instrumented step for ray counts and per-kernel device times (CUDA events inside the library)
     barrier()
     st = step(True)
     barrier()
@@ -225,27 +451,25 @@ def run_ours(args):
         dist.all_reduce(counts, op=dist.ReduceOp.SUM)
     rays, paths, launches, queue_bytes = counts.tolist()
 
-    # end-to-end through the host-buffer C ABI: scene upload + render + image download, every step
+    # end-to-end through the host-buffer C ABI: scene upload + render + image download, EVERY step, over
+    # the same number of steps as `value`
     h2d = sum(4 * 4 * flat.desc.images[i].width * flat.desc.images[i].height for i in range(flat.desc.n_images))
     h2d += 32 * flat.desc.n_prims + 96 * flat.desc.n_xforms + 4 * flat.desc.n_ops + 32 * flat.desc.n_materials + 8 * flat.desc.n_texops + 4 * flat.desc.n_texdata
-    e2e_steps = max(1, min(args.steps, 2))
-    host_np = host_image.numpy()
-
+    e2e_steps = args.steps
     e2e_parts = [0.0, 0.0, 0.0]  # scene create, render + download, destroy (host clock, rank 0's own)
+    params_e2e = make_params(spp=spp)
 
     def e2e_step():
         t_a = time.perf_counter()
-        sc2 = device.DeviceScene(flat)
-        t_b = time.perf_counter()
-        if world_size == 1:
-            sc2.render(params, host_np)
+        if comm is None:
+            sc2 = device.DeviceScene(flat)
         else:
-            accum.zero_()
-            sc2.render_accumulate(params, accum, stream, False)
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
-            if rank == 0:
-                device.resolve(accum, rgba, stream)
-                host_image.copy_(rgba, non_blocking=True)
+            sc2 = comm.create_scene(flat)  # rank 0 uploads the images once, NCCL broadcast to the others over NVLink
+        t_b = time.perf_counter()
+        if comm is None:
+            sc2.render(params_e2e, host_np)
+        else:
+            comm.render(sc2, params_e2e, None, host_np, False, stream)  # every rank downloads its own rows
         torch.cuda.synchronize()
         t_c = time.perf_counter()
         sc2.close()
@@ -265,55 +489,91 @@ def run_ours(args):
         dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
 
     if rank != 0:
+        if comm is not None:
+            comm.close()
         if world_size > 1:
             dist.destroy_process_group()
         return
     fma_per_s, implied_mhz = device.fp32_peak()
-    fpr = flops_per_ray(flat.desc)
-    stage_ms = st.ms_primary + st.ms_bounce
-    # roofline kernel = the primary TRACE kernel (tracePrimaryKernel): its launches are timed alone with
-    # CUDA events on the render stream inside the library (PtbStats.ms_trace_primary)
-    n_trace_launches = max(1, int(st.launches) // (2 + 2 * 16))
-    trace_ms = st.ms_trace_primary
-    achieved = st.rays_primary * fpr / (trace_ms * 1e-3) / 1e12 if trace_ms > 0 else 0.0
-    traffic = None
-    try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
-    except Exception:
-        pass
-    peak = 2 * fma_per_s / 1e12
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
+    fp32_peak = 2 * fma_per_s / 1e12
+    peaks = load_json("MEASURED_PEAKS.json")
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    hbm_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "6650 GB/s (of fallback)"
+    passes = spec_total if spec_total else max(1, int(st.launches) // (2 + 2 * MAX_DEPTH))
+    kernels = kernel_rooflines(args.workload, flat.desc, st, n_pix, passes, fp32_peak, hbm_peak, spec_total > 0 and spec_passes == spec_total)
+    top = dict(max(kernels, key=lambda k: k["ms"]))
+    fpr = trace_flops_per_ray(flat.desc)
+    stage_ms = st.ms_primary + st.ms_bounce
     value = rays / (ms_per_step * 1e-3) / 1e6
+    roofline = {
+        "bound": top["bound"], "achieved": top["achieved"], "peak": top["peak"], "unit": top["unit"], "frac": top["frac"], "traffic": top["traffic"],
+        "kernel": "%s (rank 0): largest share of the step (%.0f %%), %d launches, %.3f ms average" % (top["kernel"], 100 * top["share"], top["launches"], top["ms"] / max(1, passes)),
+        "model": top["model"], "kernels": kernels,
+        "whole_wavefront_fp32": {"achieved": (st.rays * fpr + st.rays_primary * CAMERA_FLOPS + st.rays * SHADE_FLOPS) / (stage_ms * 1e-3) / 1e12 if stage_ms > 0 else 0.0, "peak": fp32_peak,
+                                 "frac": (st.rays * fpr + st.rays_primary * CAMERA_FLOPS + st.rays * SHADE_FLOPS) / (stage_ms * 1e-3) / 1e12 / fp32_peak if stage_ms > 0 and fp32_peak else None,
+                                 "stage_ms": stage_ms, "model": "trace %d + shade %d flop per ray, camera %d per path" % (fpr, SHADE_FLOPS, CAMERA_FLOPS)},
+        "peak_source": {"fp32": "ptb200_fp32_peak FMA-chain microbenchmark on this GPU (MEASURED_PEAKS.json has no FP32 entry); %.2f T lane-FMA/s = 128 lanes x %d SMs x %.0f MHz"
+                                % (fma_per_s / 1e12, torch.cuda.get_device_properties(0).multi_processor_count, implied_mhz), "hbm": hbm_src},
+        "hbm_queues": {"bound": "hbm", "achieved": queue_bytes / world_size / (stage_ms * 1e-3) / 1e9 if stage_ms > 0 else 0.0, "peak": hbm_peak, "unit": "GB/s",
+                       "frac": queue_bytes / world_size / (stage_ms * 1e-3) / 1e9 / hbm_peak if stage_ms > 0 else None, "bytes_per_ray": "16 B hit record + 176 B per queued ray (64 written, 64 + 32 read, 16 hit)"},
+    }
+    secondary = None
+    single = world_size == 1 and not args.no_secondary and args.workload == "c5"
+    if single:
+        # the other numbers the north-star is judged on, in the same driver-run line
+        secondary = {}
+        del accum, rgba
+        scene.close()
+        torch.cuda.empty_cache()
+        w4, h4, spp4, desc4 = WORKLOADS["c4"]
+        flat4 = device.Flat(build_world(product_builder(), "c4"))
+        sc4 = device.DeviceScene(flat4)
+        acc4 = torch.zeros((h4, w4, 4), device="cuda")
+        out4 = torch.empty_like(acc4)
+        steps4 = max(5, min(args.steps, 8))
+        ms4, st4 = run_render(sc4, flat4, "c4", w4, h4, spp4, steps4, 2, args.samples_per_pass, torch, stream, acc4, out4)
+        _, _, sp4, tot4 = sc4.specialized()
+        k4 = kernel_rooflines("c4", flat4.desc, st4, w4 * h4, tot4 if tot4 else max(1, int(st4.launches) // (2 + 2 * MAX_DEPTH)), fp32_peak, hbm_peak, tot4 > 0 and sp4 == tot4)
+        secondary["c4"] = {
+            "config": workload_config("c4"), "metric": "Mrays/s", "value": st4.rays / (ms4 * 1e-3) / 1e6, "unit": "Mrays/s", "steps": steps4, "warmup": 2, "ms_per_step": ms4,
+            "mpaths_per_s": st4.paths / (ms4 * 1e-3) / 1e6, "rays_per_path": st4.rays / max(1, st4.paths),
+            "roofline": {"kernels": k4, "north_star_target": "1-GPU throughput >= 40 % of FP32 issue peak on the 4K deep-CSG scene: `frac` of trace_primary is useful reference-work (trace-only model) per second over the measured FP32 peak; ncu.fma_pipe_pct is the FMA-pipe counter of the same kernel"},
+            "stage_ms": {"trace_primary": st4.ms_trace_primary, "shade_primary": st4.ms_shade_primary, "trace_bounce": st4.ms_trace_bounce, "shade_bounce": st4.ms_shade_bounce, "total": st4.ms_total},
+        }
+        if not args.no_cpu:
+            secondary["c4"]["cpu_baseline"] = cpu_reference_rate("c4", float(os.environ.get("PTB200_REF_SECONDS_C4", "6")), w4, h4)
+        del acc4, out4
+        sc4.close()
+        torch.cuda.empty_cache()
+        secondary["c3"] = run_c3(torch, 5, fp32_peak, hbm_peak, not args.no_cpu)
     cpu = cpu_reference_rate(args.workload, float(os.environ.get("PTB200_REF_SECONDS", "15")), width, height) if world_size == 1 and not args.no_cpu else None
+    config = workload_config(args.workload, spp)
     out = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "width": width, "height": height, "spp": spp, "max_depth": 16, "samples_per_pass": args.samples_per_pass or "auto",
-                   "parallelism": "spp-sharded x%d + NCCL sum-reduce" % world_size if world_size > 1 else "1 GPU",
-                   "l2": "accumulation buffer (133 MB) is rewritten and the ray queues (GBs) stream through HBM every step: working set >> 126 MB L2"},
+        "config": config,
+        "parallelism": "spp-sharded x%d, ptb200_render_multi: NCCL reduce-scatter of row blocks + per-rank resolve" % world_size if world_size > 1 else "1 GPU",
+        "samples_per_pass": args.samples_per_pass or "auto",
         "mpaths_per_s": paths / (ms_per_step * 1e-3) / 1e6, "rays_per_path": rays / paths,
-        "e2e": {"value": rays / (e2e_ms.item() * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms.item(), "parts_ms": {"scene_create": e2e_parts[0], "render_and_download": e2e_parts[1], "destroy": e2e_parts[2]}, "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": width * height * 16, "what": "ptb200_scene_create (uploads scene + images) + ptb200_render into a host buffer + destroy, per step"},
-        "gpu_launches": int(launches / world_size) * args.steps + args.steps * (1 if rank == 0 else 0),
+        "e2e": {"value": rays / (e2e_ms.item() * 1e-3) / 1e6, "unit": "Mrays/s", "steps": e2e_steps, "ms_per_step": e2e_ms.item(),
+                "parts_ms": {"scene_create": e2e_parts[0], "render_and_download": e2e_parts[1], "destroy": e2e_parts[2]}, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": width * height * 16,
+                "what": "ptb200_scene_create (uploads scene + images) + ptb200_render into a host buffer + destroy, per step" if world_size == 1 else
+                        "ptb200_scene_create_multi (rank 0 uploads, NCCL broadcast of the images) + ptb200_render_multi (every rank downloads its own rows into host memory) + destroy, per step"},
+        "gpu_launches": int(launches / world_size) * args.steps + args.steps,
         "clocks": sampler.summary(),
-        "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic,
-                     "kernel": ("ptbSpecTracePrimary (scene-specialised, NVRTC)" if spec_passes == spec_total and spec_total else "tracePrimaryKernel") + " (rank 0): %d launches, %.3f ms average, %.0f Mrays/s" % (n_trace_launches, trace_ms / n_trace_launches, st.rays_primary / (trace_ms * 1e-3) / 1e6 if trace_ms > 0 else 0.0),
-                     "flops_per_ray_model": fpr, "whole_wavefront": {"achieved": st.rays * fpr / (stage_ms * 1e-3) / 1e12 if stage_ms > 0 else 0.0, "stage_ms": stage_ms},
-                     "peak_source": "ptb200_fp32_peak FMA-chain microbenchmark on this GPU (MEASURED_PEAKS.json has no FP32 entry); %.2f T lane-FMA/s = 128 lanes x %d SMs x %.0f MHz" % (fma_per_s / 1e12, torch.cuda.get_device_properties(0).multi_processor_count, implied_mhz),
-                     "hbm_queues": {"bound": "hbm", "achieved": queue_bytes / world_size / (stage_ms * 1e-3) / 1e9 if stage_ms > 0 else 0.0, "peak": hbm_peak, "unit": "GB/s",
-                                    "frac": queue_bytes / world_size / (stage_ms * 1e-3) / 1e9 / hbm_peak if stage_ms > 0 else None, "bytes_per_ray": "16 B hit record + 176 B per queued ray (64 written, 64 + 32 read, 16 hit)"}},
+        "roofline": roofline,
         "trace_kernels": {"specialized_passes": spec_passes, "passes": spec_total, "nvrtc_compile_ms": spec_compile_ms if spec_ready else None,
                           "policy": os.environ.get("PTB_SPECIALIZE", "auto: programs <= 96 words, compiled in the background during warm-up")},
-        "stage_ms": {"primary": st.ms_primary, "bounce": st.ms_bounce, "total": st.ms_total, "trace_primary": st.ms_trace_primary, "trace_bounce": st.ms_trace_bounce},
+        "stage_ms": {"primary": st.ms_primary, "bounce": st.ms_bounce, "total": st.ms_total, "trace_primary": st.ms_trace_primary, "shade_primary": st.ms_shade_primary,
+                     "trace_bounce": st.ms_trace_bounce, "shade_bounce": st.ms_shade_bounce},
+        "secondary": secondary,
         "cpu_baseline": cpu,
     }
     sys.stdout.flush()
     os.write(json_fd, (json.dumps(out) + "\n").encode())
+    if comm is not None:
+        comm.close()
     if world_size > 1:
         dist.destroy_process_group()
 
@@ -327,7 +587,8 @@ def main():
     ap.add_argument("--workload", default="c5", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel (parity/debug runs only)")
     ap.add_argument("--samples-per-pass", type=int, default=0)
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the secondary c4 / c3 legs")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

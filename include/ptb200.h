@@ -33,7 +33,7 @@ typedef unsigned long long uint64_t;
 extern "C" {
 #endif
 
-#define PTB200_ABI_VERSION 1
+#define PTB200_ABI_VERSION 2
 
 /* ---- status codes -------------------------------------------------------------------------- */
 enum {
@@ -138,7 +138,12 @@ typedef struct PtbSceneDesc {
     const PtbImageDesc *images;
 } PtbSceneDesc;
 
-typedef struct PtbScene PtbScene; /* opaque; immutable after create, shareable between threads */
+/* Opaque.  The scene data is immutable after create.  Calls on one scene are serialised: a scene owns ONE set of
+ * device scratch (ray queues, hit records, counters, span-pool overflow), so a call first waits — on the device,
+ * cudaStreamWaitEvent — for the previous call on that scene if it ran on another stream, and the host side is
+ * guarded by a mutex.  Threads may share a scene; for calls that overlap on the GPU create one scene per stream.
+ * ptb200_scene_destroy waits for the last call on the scene to finish. */
+typedef struct PtbScene PtbScene;
 
 /* ---- ray-batch intersection (BASELINE config 3) --------------------------------------------- */
 
@@ -208,6 +213,11 @@ typedef struct PtbStats {
     uint64_t rays_bounce;    /* rays traced by the bounce kernels                                  */
     float ms_trace_primary;  /* ... of the primary TRACE kernel alone (the roofline kernel)        */
     float ms_trace_bounce;   /* ... of the bounce TRACE kernels alone                              */
+    /* ABI 2 */
+    uint64_t rays_first_bounce; /* survivors of the primary shade = rays of bounce level 1          */
+    uint64_t launches_elided;   /* trace/shade launches not made because the level's queue was empty */
+    float ms_shade_primary;  /* ... of the primary SHADE kernel alone                              */
+    float ms_shade_bounce;   /* ... of the bounce SHADE kernels alone                              */
 } PtbStats;
 
 /* ---- entry points --------------------------------------------------------------------------- */
@@ -307,6 +317,41 @@ int ptb200_job_read(PtbJob *job, float *rgba, int width, int height);
 int ptb200_job_wait(PtbJob *job, PtbStats *stats);
 void ptb200_job_destroy(PtbJob *job);
 
+/* ---- multi-GPU: sample-sharded rendering with ONE NCCL exchange step ---------------------------------
+ * Replaces the reference's tile farm seam (NetRenderBlock client, src/test.cpp:520-630; server(),
+ * :681-778): there a C++ main hands 32x32 tiles to render servers over TCP; here rank g of G renders the
+ * global camera-sample indices g, g+G, ... of EVERY pixel (the RNG is keyed by the global index, so the
+ * union over ranks is exactly the one-GPU sample set), then one ncclReduceScatter of the accumulation frame
+ * by row blocks over NVLink, and every rank divides and delivers its own rows.  libnccl.so.2 is loaded on
+ * first use.  PTB_ENODEV when NCCL is missing.
+ *
+ * _comm_init_all: ONE process drives n devices (devices == NULL: 0..n-1), ncclCommInitAll, one host thread
+ *   and stream per device per frame; calls on such a communicator are synchronous.
+ * _comm_unique_id / _comm_init_rank: one process per GPU (torchrun, MPI); rank 0 makes the 128-byte id, the
+ *   caller ships it; the member lives on the CUDA device current at the call.
+ * _scene_create_multi: the scene on every LOCAL member, scenes[0..nlocal).  Image pixels cross PCIe once (rank
+ *   0; other ranks may pass rgba == NULL in PtbImageDesc) and reach the other GPUs by ncclBroadcast.  Collective.
+ * _render_multi: one whole frame of params->spp samples over all ranks.  Collective.  rgba_out (host,
+ *   width*height*4 floats, nullable): every local member writes ITS rows (ptb200_multi_rows) — the whole image in
+ *   init_all mode, this rank's row block in init_rank mode.  d_rgba_out (nullable): per local member a device
+ *   image of width*height float4 on that member's device; its own rows are written.  stats (nullable): nlocal
+ *   entries.  stream: init_rank mode only (NULL = default); asynchronous there unless rgba_out or stats is given.
+ * _multi_rows / _multi_shard: the partition rules (pure functions, no GPU): rank r owns rows
+ *   [r*ceil(H/G), min(H, (r+1)*ceil(H/G))) and samples r, r+G, ... below spp. */
+#define PTB_COMM_ID_BYTES 128
+typedef struct PtbComm PtbComm;
+#ifndef __CUDACC_RTC__
+int ptb200_comm_unique_id(void *id);
+int ptb200_comm_init_rank(const void *id, int rank, int nranks, PtbComm **out);
+int ptb200_comm_init_all(const int *devices, int n, PtbComm **out);
+int ptb200_comm_info(const PtbComm *comm, int *nranks, int *nlocal, int *first_rank);
+void ptb200_comm_destroy(PtbComm *comm);
+int ptb200_scene_create_multi(PtbComm *comm, const PtbSceneDesc *desc, PtbScene **scenes);
+int ptb200_render_multi(PtbComm *comm, PtbScene *const *scenes, const PtbRenderParams *params, float *rgba_out, void *const *d_rgba_out, PtbStats *stats, void *stream);
+int ptb200_multi_rows(int height, int nranks, int rank, int *row0, int *row1);
+int ptb200_multi_shard(int spp, int nranks, int rank, int *count, int *offset, int *stride);
+#endif
+
 /* Scene-specialised trace kernels.  The CSG program of a scene is also printed as straight-line CUDA
  * (every header, matrix and plane a literal) and compiled for sm_100a at run time with NVRTC; the trace
  * kernels built from it compute exactly what the interpreting ones do with about half the instructions.
@@ -342,6 +387,17 @@ int ptb200_tile_decode(const char *text, size_t length, int x, int y, int size, 
  * one unit normal, un-normalised mirror vector and scatter coefficient (reference
  * include/path-trace.h:140-158); (0,0,0) marks a dropped vertex.  For statistical checks. */
 int ptb200_sample_scatter(const float *normal, const float *mirror, float scatter, size_t n, uint64_t seed, uint32_t flags, float *dirs);
+
+/* Vector3D::reflect / refract / refractStrength (reference include/vector3d.h:186-214) as the shade kernel
+ * computes them, for known-answer tests.  v, normal: n x 3 floats; ior: n floats (op 1, 2).
+ * op 0 reflect -> out n x 3; 1 refract -> out n x 3; 2 refractStrength -> out n. */
+int ptb200_vector_eval(int op, const float *v, const float *normal, const float *ior, size_t n, float *out);
+/* The random words the render kernels draw in place of the reference's shared LCG (DefaultRandomEngine,
+ * include/path-trace.h:21-54; parity is statistical), for statistical tests.  which 0: the
+ * sub-pixel jitter hash of camera sample (pixel[i], sample[i]) -> out 2 words per entry; which 1: Philox4x32-10
+ * block block[i] (NULL: block 0) of that sample's stream -> out 4 words per entry.  A word w maps to [0,1] as
+ * float(w) / 2^32, the reference's uniform_real_distribution (include/vector3d.h:26-33). */
+int ptb200_rng_words(int which, uint64_t seed, const uint32_t *pixel, const uint32_t *sample, const uint32_t *block, size_t n, uint32_t *out);
 
 /* FP32 FMA-chain microbenchmark on the current device: measured lane-FMA/s (the FP32 issue-peak
  * denominator of the roofline). */

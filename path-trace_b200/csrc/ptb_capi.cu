@@ -12,28 +12,28 @@
 #include <thread>
 #include <vector>
 
-#include "ptb_launch.h"
+#include "ptb_internal.h"
 #include "ptb_csg_fast.cuh"
-#include "ptb_specialize.h"
 
 using namespace ptb;
 
+namespace ptb
+{
 namespace
 {
 thread_local std::string g_error;
+}
 int fail(int code, const std::string &msg)
 {
     g_error = msg;
     return code;
 }
-#define CU(call)                                                                                           \
-    do                                                                                                     \
-    {                                                                                                      \
-        cudaError_t e_ = (call);                                                                           \
-        if(e_ != cudaSuccess)                                                                              \
-            return fail(PTB_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_));                    \
-    } while(0)
+const std::string &lastError() { return g_error; }
+void setLastError(const std::string &msg) { g_error = msg; }
+} // namespace ptb
 
+namespace
+{
 // Scratch blocks are cached per process instead of going back to the driver: cudaMalloc / cudaFree of
 // the multi-GB ray queues cost from milliseconds to seconds (cudaFree synchronises the device and
 // unmaps) and a renderer that creates and destroys scenes per frame would pay that every frame.
@@ -55,13 +55,26 @@ struct CachedArray
     int w, h, device;
 };
 static std::vector<CachedArray> g_arrayCache;
-// Pinned staging for host -> array uploads from pageable memory (two halves, used alternately).
+// Pinned staging for host -> device uploads from pageable memory (two halves, used alternately).
 static std::mutex g_stagingLock;
 static char *g_staging = nullptr;
 static const size_t kStagingHalf = size_t(8) << 20;
 static cudaEvent_t g_stagingDone[2] = {nullptr, nullptr};
+static int stagingInit()
+{
+    if(!g_staging)
+    {
+        CU(cudaMallocHost((void **)&g_staging, 2 * kStagingHalf));
+        CU(cudaEventCreateWithFlags(&g_stagingDone[0], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&g_stagingDone[1], cudaEventDisableTiming));
+    }
+    return PTB_OK;
+}
+} // namespace
 
-static void cacheTrim(int device)
+namespace ptb
+{
+void cacheTrim(int device)
 { // device < 0: every device
     std::vector<CachedBlock> drop;
     std::vector<CachedArray> dropArrays;
@@ -101,124 +114,110 @@ static void cacheTrim(int device)
     cudaSetDevice(current);
 }
 
-struct DeviceBuffer
+void DeviceBuffer::release()
 {
-    void *p = nullptr;
-    size_t bytes = 0;
-    int device = 0;
-    ~DeviceBuffer() { release(); }
-    void release()
+    if(p)
     {
-        if(p)
+        if(bytes >= (1u << 20))
         {
-            if(bytes >= (1u << 20))
-            {
-                std::lock_guard<std::mutex> g(g_cacheLock);
-                g_cache.push_back(CachedBlock{p, bytes, device});
-            }
-            else
-                cudaFree(p);
-        }
-        p = nullptr, bytes = 0;
-    }
-    cudaError_t ensure(size_t n)
-    {
-        if(n <= bytes)
-            return cudaSuccess;
-        release();
-        cudaError_t e = cudaGetDevice(&device);
-        if(e != cudaSuccess)
-            return e;
-        { // best fit among the cached blocks of this device, at most twice the size asked for
             std::lock_guard<std::mutex> g(g_cacheLock);
-            size_t best = g_cache.size();
-            for(size_t i = 0; i < g_cache.size(); i++)
-                if(g_cache[i].device == device && g_cache[i].bytes >= n && g_cache[i].bytes / 2 <= n && (best == g_cache.size() || g_cache[i].bytes < g_cache[best].bytes))
-                    best = i;
-            if(best != g_cache.size())
-            {
-                p = g_cache[best].p, bytes = g_cache[best].bytes;
-                g_cache[best] = g_cache.back();
-                g_cache.pop_back();
-                return cudaSuccess;
-            }
+            g_cache.push_back(CachedBlock{p, bytes, device});
         }
-        e = cudaMalloc(&p, n);
-        if(e != cudaSuccess)
-        {
-            cudaGetLastError();
-            cacheTrim(device);
-            e = cudaMalloc(&p, n);
-        }
-        if(e == cudaSuccess)
-            bytes = n;
         else
-            p = nullptr;
+            cudaFree(p);
+    }
+    p = nullptr, bytes = 0;
+}
+cudaError_t DeviceBuffer::ensure(size_t n)
+{
+    if(n <= bytes)
+        return cudaSuccess;
+    release();
+    cudaError_t e = cudaGetDevice(&device);
+    if(e != cudaSuccess)
         return e;
+    { // best fit among the cached blocks of this device, at most twice the size asked for
+        std::lock_guard<std::mutex> g(g_cacheLock);
+        size_t best = g_cache.size();
+        for(size_t i = 0; i < g_cache.size(); i++)
+            if(g_cache[i].device == device && g_cache[i].bytes >= n && g_cache[i].bytes / 2 <= n && (best == g_cache.size() || g_cache[i].bytes < g_cache[best].bytes))
+                best = i;
+        if(best != g_cache.size())
+        {
+            p = g_cache[best].p, bytes = g_cache[best].bytes;
+            g_cache[best] = g_cache.back();
+            g_cache.pop_back();
+            return cudaSuccess;
+        }
     }
-};
-
-struct ImageSlot
-{
-    cudaArray_t array = nullptr;
-    cudaTextureObject_t point = 0, linear = 0;
-    int w = 0, h = 0;
-};
-
-// Per-scene scratch for rendering (queues, counters, events); guarded by `busy`.
-struct RenderScratch
-{
-    DeviceBuffer queues, hits, counters, overflow, accum;
-    DeviceBuffer adaptive; // value + interp frames, request flags, square and pixel lists of ptb200_render_adaptive
-    unsigned *hostCounters = nullptr; // pinned
-    size_t hostCountersLen = 0;
-    std::vector<cudaEvent_t> events;
-    ~RenderScratch()
+    e = cudaMalloc(&p, n);
+    if(e != cudaSuccess)
     {
-        if(hostCounters)
-            cudaFreeHost(hostCounters);
-        for(cudaEvent_t e : events)
-            cudaEventDestroy(e);
+        cudaGetLastError();
+        cacheTrim(device);
+        e = cudaMalloc(&p, n);
     }
-};
-} // namespace
+    if(e == cudaSuccess)
+        bytes = n;
+    else
+        p = nullptr;
+    return e;
+}
 
-struct PtbScene
+RenderScratch::~RenderScratch()
 {
-    int device = 0;
-    int smCount = 148;
-    size_t smemOptin = 0;
-    DevScene dev;
-    std::vector<void *> allocs;
-    std::vector<ImageSlot> images;
-    DevImage *dImages = nullptr;
-    int imageCapacity = 0;
-    std::mutex lock; // one render / intersect call at a time per scene
-    RenderScratch scratch;
-    bool asyncBusy = false;
-    // scene-specialised trace kernels (ptb_specialize.cu): compiled on first use by a render or ray batch
-    // large enough to pay for the compile, or at once with PTB_FLAG_SPECIALIZE
-    std::vector<uint4> fastHost;
-    std::string specSource[2]; // SPEC_TRACE, SPEC_INTERSECT
-    int lastSpecPasses = 0, lastPasses = 0; // of the last render call with stats
-    const SpecKernels *spec = nullptr;
-    bool specTried = false;
-    DeviceBuffer specOverflow;
-};
+    if(hostCounters)
+        cudaFreeHost(hostCounters);
+    for(cudaEvent_t e : events)
+        cudaEventDestroy(e);
+}
 
-struct PtbJob
+// Host -> linear device memory from a pageable buffer, through the pinned staging halves: the CPU copy of
+// piece k+1 overlaps the DMA of piece k (the driver's own pageable path ran at < 2 GB/s here).
+int uploadLinear(void *dst, const void *src, size_t bytes)
 {
-    PtbScene *scene = nullptr;
-    PtbRenderParams params;
-    std::thread worker;
-    volatile int done = 0;
-    int status = 0;
-    std::string error;
-    PtbStats stats;
-    cudaStream_t readStream = nullptr;
-    float4 *accum = nullptr; // device, owned by the job
-    std::vector<float> staging;
-};
+    std::lock_guard<std::mutex> g(g_stagingLock);
+    if(int rc = stagingInit())
+        return rc;
+    int k = 0;
+    for(size_t at = 0; at < bytes; at += kStagingHalf, k ^= 1)
+    {
+        const size_t n = std::min(kStagingHalf, bytes - at);
+        CU(cudaEventSynchronize(g_stagingDone[k])); // the copy that last used this half has finished
+        memcpy(g_staging + k * kStagingHalf, (const char *)src + at, n);
+        CU(cudaMemcpyAsync((char *)dst + at, g_staging + k * kStagingHalf, n, cudaMemcpyHostToDevice, nullptr));
+        CU(cudaEventRecord(g_stagingDone[k], nullptr));
+    }
+    CU(cudaStreamSynchronize(nullptr));
+    return PTB_OK;
+}
+} // namespace ptb
+
+// ---- device-side ordering of a scene's shared scratch ---------------------------------------------------
+int PtbScene::begin(cudaStream_t stream)
+{
+    if(!lastUse)
+        CU(cudaEventCreateWithFlags(&lastUse, cudaEventDisableTiming));
+    if(lastUsePending && stream != lastUseStream)
+        CU(cudaStreamWaitEvent(stream, lastUse, 0)); // the previous call (another stream) still owns queues, hits, counters, overflow
+    return PTB_OK;
+}
+int PtbScene::end(cudaStream_t stream)
+{
+    if(!lastUse)
+        CU(cudaEventCreateWithFlags(&lastUse, cudaEventDisableTiming));
+    CU(cudaEventRecord(lastUse, stream));
+    lastUseStream = stream, lastUsePending = true;
+    return PTB_OK;
+}
+void PtbScene::quiesce()
+{
+    if(lastUse && lastUsePending)
+    {
+        cudaEventSynchronize(lastUse);
+        lastUsePending = false;
+    }
+}
 
 namespace
 {
@@ -236,9 +235,10 @@ int upload(PtbScene *s, const std::vector<T> &host, const T **out)
     return PTB_OK;
 }
 
-int createImage(const float *rgba, int w, int h, ImageSlot &slot)
+// deviceLinear != NULL: the pixels are already on this device as a linear RGBA32F buffer (multi-GPU create)
+int createImage(const float *rgba, int w, int h, ImageSlot &slot, const float4 *deviceLinear = nullptr)
 {
-    if(!rgba || w <= 0 || h <= 0)
+    if((!rgba && !deviceLinear) || w <= 0 || h <= 0)
         return fail(PTB_EINVAL, "image with no pixels");
     cudaChannelFormatDesc fmt = cudaCreateChannelDesc<float4>();
     int device = 0;
@@ -258,18 +258,16 @@ int createImage(const float *rgba, int w, int h, ImageSlot &slot)
         CU(cudaMallocArray(&slot.array, &fmt, (size_t)w, (size_t)h));
     slot.w = w, slot.h = h;
     const size_t rowBytes = (size_t)w * 16;
-    if((size_t)h * rowBytes < (size_t(1) << 20) || rowBytes > kStagingHalf)
+    if(deviceLinear)
+        CU(cudaMemcpy2DToArray(slot.array, 0, 0, deviceLinear, rowBytes, rowBytes, (size_t)h, cudaMemcpyDeviceToDevice));
+    else if((size_t)h * rowBytes < (size_t(1) << 20) || rowBytes > kStagingHalf)
         CU(cudaMemcpy2DToArray(slot.array, 0, 0, rgba, rowBytes, rowBytes, (size_t)h, cudaMemcpyHostToDevice));
     else
     { // the caller's buffer is pageable: copy it through pinned staging in 8 MB pieces, the CPU copy of
       // piece k+1 overlapping the DMA of piece k (the driver's own pageable path ran at < 2 GB/s here)
         std::lock_guard<std::mutex> g(g_stagingLock);
-        if(!g_staging)
-        {
-            CU(cudaMallocHost((void **)&g_staging, 2 * kStagingHalf));
-            CU(cudaEventCreateWithFlags(&g_stagingDone[0], cudaEventDisableTiming));
-            CU(cudaEventCreateWithFlags(&g_stagingDone[1], cudaEventDisableTiming));
-        }
+        if(int rc = stagingInit())
+            return rc;
         const int rowsPerPiece = (int)(kStagingHalf / rowBytes);
         int k = 0;
         for(int y = 0; y < h; y += rowsPerPiece, k ^= 1)
@@ -370,7 +368,7 @@ int validateTexture(const PtbSceneDesc *d, int root)
 } // namespace
 
 // ---- scene ------------------------------------------------------------------------------------
-extern "C" const char *ptb200_last_error(void) { return g_error.c_str(); }
+extern "C" const char *ptb200_last_error(void) { return lastError().c_str(); }
 extern "C" int ptb200_abi_version(void) { return PTB200_ABI_VERSION; }
 extern "C" int ptb200_trim(void)
 {
@@ -709,7 +707,7 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
     }
 }
 
-static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> *fastOnly = nullptr)
+int ptb::sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> *fastOnly, const std::vector<ImageSource> *sources)
 {
     if(!d || d->abi_version != PTB200_ABI_VERSION)
         return fail(PTB_EINVAL, "scene description has a different abi_version");
@@ -889,7 +887,7 @@ static int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4
     for(int i = 0; i < d->n_images; i++)
     {
         ImageSlot slot;
-        if((rc = createImage(d->images[i].rgba, d->images[i].width, d->images[i].height, slot)))
+        if((rc = createImage(d->images[i].rgba, d->images[i].width, d->images[i].height, slot, sources && (size_t)i < sources->size() ? (*sources)[i].device : nullptr)))
             return rc;
         s->images.push_back(slot);
     }
@@ -901,6 +899,9 @@ extern "C" void ptb200_scene_destroy(PtbScene *s)
     if(!s)
         return;
     cudaSetDevice(s->device);
+    s->quiesce(); // an asynchronous accumulate / ray batch may still be reading the textures and the scratch
+    if(s->lastUse)
+        cudaEventDestroy(s->lastUse);
     for(ImageSlot &im : s->images)
     {
         if(im.point)
@@ -944,9 +945,9 @@ extern "C" int ptb200_scene_create(const PtbSceneDesc *desc, PtbScene **out)
         int rc = sceneCreateImpl(desc, s);
         if(rc)
         {
-            std::string keep = g_error;
+            std::string keep = lastError();
             ptb200_scene_destroy(s);
-            g_error = keep;
+            setLastError(keep);
             return rc;
         }
         *out = s;
@@ -979,6 +980,14 @@ extern "C" int ptb200_image_upload(PtbScene *s, const float *rgba, int width, in
 // ---- launch configuration -----------------------------------------------------------------------
 // Persistent grid: (resident CTAs per SM) x (SM count).  The span pool keeps `cap` slots per
 // thread in shared memory; scenes whose worst case needs more get a global overflow area.
+// Scratch shared by the calls on a scene only changes hands once the last call that used it has finished.
+static cudaError_t ensureScratch(PtbScene *s, DeviceBuffer &b, size_t n)
+{
+    if(n > b.bytes)
+        s->quiesce();
+    return b.ensure(n);
+}
+
 static int chooseConfig(PtbScene *s, int which, DeviceBuffer &overflow, CsgConfig &cfg)
 {
     const DevScene &dev = s->dev;
@@ -1012,7 +1021,7 @@ static int chooseConfig(PtbScene *s, int which, DeviceBuffer &overflow, CsgConfi
     if(dev.poolBound > cfg.cap)
     {
         size_t bytes = (size_t)rays * (dev.poolBound - cfg.cap) * 3 * sizeof(float) * cfg.ovfStride;
-        CU(overflow.ensure(bytes));
+        CU(ensureScratch(s, overflow, bytes));
         cfg.overflow = (float *)overflow.p;
     }
     return PTB_OK;
@@ -1084,7 +1093,7 @@ static int chooseSpec(PtbScene *s, uint32_t flags, double work, int which, SpecC
     cfg.overflow = nullptr;
     if(dev.poolBound > cfg.cap)
     {
-        CU(s->specOverflow.ensure((size_t)(dev.poolBound - cfg.cap) * 3 * sizeof(float) * cfg.ovfStride));
+        CU(ensureScratch(s, s->specOverflow, (size_t)(dev.poolBound - cfg.cap) * 3 * sizeof(float) * cfg.ovfStride));
         cfg.overflow = (float *)s->specOverflow.p;
     }
     sp.k = k;
@@ -1118,6 +1127,8 @@ extern "C" int ptb200_intersect_device(PtbScene *s, const void *d_origins4, cons
     SpecConfig sp;
     if(int rc = chooseSpec(s, flags, (double)n, SPEC_INTERSECT, sp))
         return rc;
+    if(int rc = s->begin((cudaStream_t)stream))
+        return rc;
     if(sp.k)
     {
         DevScene dev = s->dev;
@@ -1126,11 +1137,11 @@ extern "C" int ptb200_intersect_device(PtbScene *s, const void *d_origins4, cons
         size_t ovfStride = sp.cfg.ovfStride;
         SPEC_LAUNCH((flags & PTB_FLAG_ORIGIN0) ? sp.k->intersectO0 : sp.k->intersect, sp.cfg, (cudaStream_t)stream, &dev, &cap, &ovf, &ovfStride, (void *)&d_origins4, (void *)&d_dirs4, &n,
                     &d_hits, &d_spans, &max_spans);
-        return PTB_OK;
+        return s->end((cudaStream_t)stream);
     }
     launchIntersect(s->dev, cfg, (const float4 *)d_origins4, (const float4 *)d_dirs4, n, (PtbHit *)d_hits, (PtbSpan *)d_spans, max_spans, exact, (flags & PTB_FLAG_ORIGIN0) != 0, (cudaStream_t)stream);
     CU(cudaGetLastError());
-    return PTB_OK;
+    return s->end((cudaStream_t)stream);
 }
 
 extern "C" int ptb200_intersect(PtbScene *s, const float *origins, const float *dirs, size_t n, PtbHit *hits, PtbSpan *spans, int max_spans, uint32_t flags)
@@ -1265,6 +1276,56 @@ extern "C" int ptb200_sample_scatter(const float *normal, const float *mirror, f
     return PTB_OK;
 }
 
+extern "C" int ptb200_vector_eval(int op, const float *v, const float *normal, const float *ior, size_t n, float *out)
+{
+    if(op < 0 || op > 2 || (n && (!v || !normal || !out || (op != 0 && !ior))))
+        return fail(PTB_EINVAL, "bad op or null argument");
+    int nDev = 0;
+    if(cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0)
+        return fail(PTB_ENODEV, "no CUDA device: libptb200 has no CPU fallback");
+    if(n == 0)
+        return PTB_OK;
+    DeviceBuffer bv, bn, bi, bo;
+    const size_t outFloats = op == 2 ? n : 3 * n;
+    CU(bv.ensure(n * 12));
+    CU(bn.ensure(n * 12));
+    CU(bi.ensure(n * 4));
+    CU(bo.ensure(outFloats * 4));
+    CU(cudaMemcpy(bv.p, v, n * 12, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(bn.p, normal, n * 12, cudaMemcpyHostToDevice));
+    if(ior)
+        CU(cudaMemcpy(bi.p, ior, n * 4, cudaMemcpyHostToDevice));
+    launchVectorEval(op, (const float *)bv.p, (const float *)bn.p, (const float *)bi.p, n, (float *)bo.p, nullptr);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(out, bo.p, outFloats * 4, cudaMemcpyDeviceToHost));
+    return PTB_OK;
+}
+
+extern "C" int ptb200_rng_words(int which, uint64_t seed, const uint32_t *pixel, const uint32_t *sample, const uint32_t *block, size_t n, uint32_t *out)
+{
+    if(which < 0 || which > 1 || (n && (!pixel || !sample || !out)))
+        return fail(PTB_EINVAL, "bad generator or null argument");
+    int nDev = 0;
+    if(cudaGetDeviceCount(&nDev) != cudaSuccess || nDev == 0)
+        return fail(PTB_ENODEV, "no CUDA device: libptb200 has no CPU fallback");
+    if(n == 0)
+        return PTB_OK;
+    const size_t words = which == 0 ? 2 * n : 4 * n;
+    DeviceBuffer bp, bs, bb, bo;
+    CU(bp.ensure(n * 4));
+    CU(bs.ensure(n * 4));
+    CU(bb.ensure(n * 4));
+    CU(bo.ensure(words * 4));
+    CU(cudaMemcpy(bp.p, pixel, n * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(bs.p, sample, n * 4, cudaMemcpyHostToDevice));
+    if(block)
+        CU(cudaMemcpy(bb.p, block, n * 4, cudaMemcpyHostToDevice));
+    launchRngWords(which, seed, (const uint32_t *)bp.p, (const uint32_t *)bs.p, block ? (const uint32_t *)bb.p : nullptr, n, (uint32_t *)bo.p, nullptr);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(out, bo.p, words * 4, cudaMemcpyDeviceToHost));
+    return PTB_OK;
+}
+
 extern "C" int ptb200_fp32_peak(double *fma_per_second, double *sm_clock_mhz)
 {
     int nDev = 0, dev = 0;
@@ -1299,7 +1360,7 @@ extern "C" int ptb200_fp32_peak(double *fma_per_second, double *sm_clock_mhz)
 }
 
 // ---- wavefront render driver ------------------------------------------------------------------------
-static int checkParams(const PtbRenderParams *p, int &x0, int &y0, int &rw, int &rh)
+int ptb::checkParams(const PtbRenderParams *p, int &x0, int &y0, int &rw, int &rh)
 {
     if(!p)
         return fail(PTB_EINVAL, "null render params");
@@ -1317,16 +1378,8 @@ static int checkParams(const PtbRenderParams *p, int &x0, int &y0, int &rw, int 
     return PTB_OK;
 }
 
-// Adaptive rendering traces explicit lists of lattice points instead of a rectangle.
-struct PixelListArg
-{
-    const uint32_t *list; // device: y << 16 | x
-    unsigned count;
-    int pitch;            // lattice points per row of the accumulation frame
-};
-
 // Caller holds scene->lock and has made scene->device current.
-static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbStats *stats, cudaStream_t stream, const PixelListArg *points = nullptr)
+int ptb::renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbStats *stats, cudaStream_t stream, const PixelListArg *points)
 {
     int x0, y0, rw, rh;
     if(int rc = checkParams(p, x0, y0, rw, rh))
@@ -1341,32 +1394,57 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
     int perPass = p->samples_per_pass;
     if(perPass <= 0)
     { // PTB_PATHS_IN_FLIGHT (default 128 Mi: 16 samples per pixel at 3840x2160; measured +11 % from 1 to 8
-      // samples per pass and +2 % from 8 to 16 — the 34 launches of a pass, half of them on nearly empty
-      // queues, are amortised), but never more than a quarter of the free HBM
+      // samples per pass and +2 % from 8 to 16 — the launches of a pass are amortised), but never more than a
+      // quarter of what the device could give: the free memory plus what this scene's queues already hold
         static const size_t inFlight = [] {
             const char *e = getenv("PTB_PATHS_IN_FLIGHT");
             long long v = e ? atoll(e) : 0;
             return v > 0 ? (size_t)v : (size_t(128) << 20);
         }();
         size_t want = inFlight, freeB = 0, totalB = 0;
-        if(cudaMemGetInfo(&freeB, &totalB) == cudaSuccess && sx.queues.bytes == 0)
-            want = std::min(want, std::max<size_t>(size_t(1) << 20, freeB / 4 / 136));
+        if(cudaMemGetInfo(&freeB, &totalB) == cudaSuccess)
+            want = std::min(want, std::max<size_t>(size_t(1) << 20, (freeB + sx.queues.bytes + sx.hits.bytes) / 4 / 136));
         perPass = (int)std::max<size_t>(1, want / nPix);
     }
     perPass = std::min(perPass, p->spp);
-    const size_t capacity = nPix * (size_t)perPass;
-    if(capacity > 0xFFFFFFF0ull)
+    if((size_t)perPass * nPix > 0xFFFFFFF0ull)
         return fail(PTB_EINVAL, "samples_per_pass x pixels exceeds the 32-bit queue index");
+    // the last global sample index must fit the kernels' 32-bit sample counter
+    if((long long)p->sample_offset + ((long long)p->spp - 1) * (long long)p->sample_stride > 0x7FFFFFFFll)
+        return fail(PTB_EINVAL, "sample_offset + (spp - 1) * sample_stride exceeds INT32_MAX");
+    size_t capacity = 0;
+    for(;;)
+    { // 136 B per path in flight (two 64 B queues + the 8 B hit record); a pass that does not fit is halved
+        capacity = nPix * (size_t)perPass;
+        if(ensureScratch(s, sx.queues, capacity * 64 * 2) == cudaSuccess && ensureScratch(s, sx.hits, capacity * sizeof(uint2)) == cudaSuccess)
+            break;
+        cudaGetLastError();
+        if(perPass == 1)
+            return fail(PTB_ENOMEM, "no device memory for the ray queues of even one sample per pixel per pass");
+        perPass = (perPass + 1) / 2;
+    }
     const int nPasses = (p->spp + perPass - 1) / perPass;
     const int stages = p->max_depth + 1; // primary + max_depth bounces
-    CU(sx.queues.ensure(capacity * 64 * 2));
-    CU(sx.hits.ensure(capacity * sizeof(uint2)));
     uint2 *hits = (uint2 *)sx.hits.p;
     const int shadePerSm = shadeBlocksPerSm(true), shadePerSmBounce = shadeBlocksPerSm(false);
     if(shadePerSm <= 0 || shadePerSmBounce <= 0)
         return fail(PTB_ECUDA, "shade kernel does not fit on an SM");
     const int shadeBlocks = shadePerSm * s->smCount, shadeBlocksBounce = shadePerSmBounce * s->smCount;
-    CU(sx.counters.ensure((size_t)nPasses * (stages + 1) * sizeof(unsigned)));
+    // Bounce levels from `tailLevel` on hold a few thousand rays at most (C5: 0.2 % of the camera rays at level
+    // 3); launched as a trace / shade pair per level they cost ~12 us each for nothing, 26 launches per pass.
+    // ONE tail kernel takes the queue of level tailLevel and follows every path to its end (trace + shade in a
+    // loop, no queue).  PTB_TAIL_LEVEL: first bounce level the tail kernel owns (0 = off: a pair per level).
+    static const int tailEnv = [] {
+        const char *e = getenv("PTB_TAIL_LEVEL");
+        return e ? atoi(e) : 3;
+    }();
+    const int tailLevel = tailEnv > 0 && tailEnv <= p->max_depth && tailBlocksPerSm(!cfg.stageProgram, cfg.smemBytes) > 0 ? tailEnv : p->max_depth + 1;
+    const int pairLevels = std::min(p->max_depth, tailLevel - 1); // bounce levels run as trace + shade pairs
+    const bool hasTail = tailLevel <= p->max_depth;
+    const int tailBlocks = hasTail ? tailBlocksPerSm(!cfg.stageProgram, cfg.smemBytes) * s->smCount : 0;
+    CU(ensureScratch(s, sx.counters, (size_t)nPasses * (stages + 1) * sizeof(unsigned)));
+    if(int rc = s->begin(stream))
+        return rc;
     CU(cudaMemsetAsync(sx.counters.p, 0, (size_t)nPasses * (stages + 1) * sizeof(unsigned), stream));
     RayQueue q[2];
     for(int k = 0; k < 2; k++)
@@ -1375,7 +1453,7 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
         q[k].q0 = base, q[k].q1 = base + capacity, q[k].q2 = base + 2 * capacity, q[k].q3 = base + 3 * capacity;
     }
     const bool timed = stats != nullptr;
-    const int evPerPass = 3 + 2 * p->max_depth; // start, trace0, shade0, then trace/shade of every bounce level
+    const int evPerPass = 3 + 2 * pairLevels + (hasTail ? 1 : 0); // start, trace0, shade0, trace/shade of every pair level, tail
     size_t nEvents = timed ? (size_t)nPasses * evPerPass : 0;
     while(sx.events.size() < nEvents)
     {
@@ -1406,7 +1484,7 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
     {
         unsigned *c = (unsigned *)sx.counters.p + (size_t)i * (stages + 1);
         pass.samplesThisPass = std::min(perPass, p->spp - i * perPass);
-        pass.sampleBase = p->sample_offset + i * perPass * p->sample_stride;
+        pass.sampleBase = (int)((long long)p->sample_offset + (long long)i * perPass * p->sample_stride);
         cudaEvent_t *ev = timed ? &sx.events[(size_t)i * evPerPass] : nullptr;
         if(timed)
             CU(cudaEventRecord(ev[0], stream));
@@ -1427,7 +1505,7 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
         launchShade(s->dev, shadeBlocks, true, pass, accum, hits, q[0], nullptr, q[0], c, stream);
         if(timed)
             CU(cudaEventRecord(ev[2], stream));
-        for(int b = 1; b <= p->max_depth; b++)
+        for(int b = 1; b <= pairLevels; b++)
         {
             if(sp.k && specBounce)
             {
@@ -1443,9 +1521,18 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
             if(timed)
                 CU(cudaEventRecord(ev[2 + 2 * b], stream));
         }
-        launches += 2 + 2 * (uint64_t)p->max_depth;
+        launches += 2 + 2 * (uint64_t)pairLevels;
+        if(hasTail)
+        { // rays of level tailLevel are in q[(tailLevel - 1) & 1], counted by c[tailLevel - 1]; rays the tail traces beyond those go to c[tailLevel]
+            launchTail(s->dev, cfg, tailBlocks, pass, accum, q[(tailLevel - 1) & 1], c + (tailLevel - 1), c + tailLevel, stream);
+            if(timed)
+                CU(cudaEventRecord(ev[evPerPass - 1], stream));
+            launches += 1;
+        }
         CU(cudaGetLastError());
     }
+    if(int rc = s->end(stream))
+        return rc;
     if(!timed)
         return PTB_OK;
     size_t nCounters = (size_t)nPasses * (stages + 1);
@@ -1459,8 +1546,10 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
     }
     CU(cudaMemcpyAsync(sx.hostCounters, sx.counters.p, nCounters * sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
     CU(cudaStreamSynchronize(stream));
+    s->lastUsePending = false;
     memset(stats, 0, sizeof(*stats));
     stats->launches = launches;
+    stats->launches_elided = (uint64_t)nPasses * (2 * (uint64_t)(p->max_depth - pairLevels) - (hasTail ? 1 : 0));
     s->lastSpecPasses = specPasses, s->lastPasses = nPasses;
     for(int i = 0; i < nPasses; i++)
     {
@@ -1471,23 +1560,30 @@ static int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, Pt
         // algorithmic HBM traffic of the wavefront: 8 B hit record written + read per ray, 64 B per
         // queued ray written by shade and read back by shade, of which trace re-reads 32 B (o, d)
         stats->queue_bytes += 16ull * primary + 64ull * c[0];
-        for(int b = 1; b <= p->max_depth; b++)
+        for(int b = 1; b <= pairLevels; b++)
         {
             stats->rays_bounce += c[b - 1];
             stats->queue_bytes += (32ull + 16ull + 64ull) * c[b - 1] + 64ull * c[b];
         }
+        if(hasTail) // the tail reads its queue once (64 B per ray) and traces c[tailLevel - 1] + c[tailLevel] rays
+            stats->rays_bounce += (uint64_t)c[tailLevel - 1] + c[tailLevel], stats->queue_bytes += 64ull * c[tailLevel - 1];
         cudaEvent_t *ev = &sx.events[(size_t)i * evPerPass];
         float ms = 0;
         CU(cudaEventElapsedTime(&ms, ev[0], ev[1]));
         stats->ms_trace_primary += ms;
         CU(cudaEventElapsedTime(&ms, ev[0], ev[2]));
         stats->ms_primary += ms;
+        CU(cudaEventElapsedTime(&ms, ev[1], ev[2]));
+        stats->ms_shade_primary += ms;
+        stats->rays_first_bounce += c[0];
         CU(cudaEventElapsedTime(&ms, ev[2], ev[evPerPass - 1]));
         stats->ms_bounce += ms;
-        for(int b = 1; b <= p->max_depth; b++)
+        for(int b = 1; b <= pairLevels; b++)
         {
             CU(cudaEventElapsedTime(&ms, ev[2 * b], ev[1 + 2 * b]));
             stats->ms_trace_bounce += ms;
+            CU(cudaEventElapsedTime(&ms, ev[1 + 2 * b], ev[2 + 2 * b]));
+            stats->ms_shade_bounce += ms;
         }
     }
     stats->rays = stats->rays_primary + stats->rays_bounce;
@@ -1531,7 +1627,7 @@ extern "C" int ptb200_render(PtbScene *s, const PtbRenderParams *p, float *rgba_
         return fail(PTB_EBUSY, "an asynchronous render is running on this scene");
     CU(cudaSetDevice(s->device));
     size_t nPix = (size_t)p->width * p->height;
-    CU(s->scratch.accum.ensure(nPix * 16));
+    CU(ensureScratch(s, s->scratch.accum, nPix * 16));
     float4 *accum = (float4 *)s->scratch.accum.p;
     CU(cudaMemsetAsync(accum, 0, nPix * 16, nullptr));
     PtbStats local;
@@ -1596,8 +1692,8 @@ extern "C" int ptb200_render_adaptive(PtbScene *s, const PtbRenderParams *p, con
                  oSqB = oSqA + align(maxSquares * 4), oList = oSqB + align(maxSquares * 4), oCnt = oList + align(nLattice * 4), oOut = oCnt + 256,
                  oSrc = oOut + align(nPix * 16), oAlt = oSrc + align(nPix), oTemp = oAlt + align(nLattice * 4),
                  sortBytes = align(adaptiveSortList(nullptr, nullptr, (unsigned)nLattice, nullptr, 0, nullptr)), total = oTemp + sortBytes;
-    CU(sx.adaptive.ensure(total));
-    CU(sx.accum.ensure(nLattice * 16));
+    CU(ensureScratch(s, sx.adaptive, total));
+    CU(ensureScratch(s, sx.accum, nLattice * 16));
     char *base = (char *)sx.adaptive.p;
     float4 *accum = (float4 *)sx.accum.p, *value = (float4 *)(base + oValue), *interp = (float4 *)(base + oInterp), *out = (float4 *)(base + oOut);
     unsigned *requested = (unsigned *)(base + oReq), *counters = (unsigned *)(base + oCnt);
@@ -1637,6 +1733,8 @@ extern "C" int ptb200_render_adaptive(PtbScene *s, const PtbRenderParams *p, con
         sum.ms_total += st.ms_total, sum.ms_primary += st.ms_primary, sum.ms_bounce += st.ms_bounce;
         sum.rays_primary += st.rays_primary, sum.rays_bounce += st.rays_bounce;
         sum.ms_trace_primary += st.ms_trace_primary, sum.ms_trace_bounce += st.ms_trace_bounce;
+        sum.ms_shade_primary += st.ms_shade_primary, sum.ms_shade_bounce += st.ms_shade_bounce;
+        sum.rays_first_bounce += st.rays_first_bounce, sum.launches_elided += st.launches_elided;
         as.pixels_traced += n;
         return PTB_OK;
     };
@@ -1723,7 +1821,7 @@ static void jobMain(PtbJob *job)
         if(rc == PTB_OK)
             rc = renderPasses(s, &job->params, job->accum, &job->stats, stream);
         if(rc != PTB_OK)
-            job->error = rc == PTB_ECUDA && g_error.empty() ? "cudaStreamCreate failed" : g_error;
+            job->error = rc == PTB_ECUDA && lastError().empty() ? "cudaStreamCreate failed" : lastError();
         if(stream)
         {
             cudaStreamSynchronize(stream);

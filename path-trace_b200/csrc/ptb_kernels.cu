@@ -180,6 +180,30 @@ __device__ __forceinline__ void accumulate(float4 *accum, uint32_t pixel, V3 rad
         atomicAdd(&accum[pixel], make_float4(rad.x, rad.y, rad.z, done));
 }
 
+// One path vertex from a packed hit record (t, kind << 16 | boundary tag): normal through the un-folded
+// transform chain, material, relative ior (path-trace.h:72-95), then shadeVertex.  Adds the vertex's radiance to
+// `rad`; true while the path goes on (ps then holds the next ray).
+__device__ __forceinline__ bool shadeHitRecord(const DevScene &sc, const RenderPass &pass, PathState &ps, uint2 h, V3 &rad)
+{
+    const int kind = (int)(h.y >> 16);
+    if(kind == PTB_HIT_MISS)
+        return false;
+    const uint32_t tag = h.y & 0xFFFFu;
+    Hit hit;
+    hit.t = __uint_as_float(h.x);
+    V3 n = boundaryNormal<false>(sc, tag, hit.t, ps.o, ps.d);
+    hit.mat = __ldg(&sc.primMeta[tag >> 1]).y;
+    if(kind == PTB_HIT_ENTER)
+        hit.n = n, hit.ior = sc.materials[hit.mat].iorIn; // path-trace.h:72-81
+    else
+        hit.n = neg(n), hit.ior = sc.materials[hit.mat].ior; // path-trace.h:86-95
+    Philox rng;
+    rngInit(rng, pass.seed, ps.pixel, ps.sample, ps.rngBlock);
+    const bool alive = shadeVertex(sc, ps, hit, rng, pass.flags, rad);
+    ps.rngBlock = rng.block;
+    return alive;
+}
+
 // Shade stage of one wavefront level: hit record -> normal, material, emitted radiance, next ray.
 // PRIMARY: path state is regenerated from the sample index; otherwise it is read from `in`.
 // Survivors are appended to `out` with __ballot_sync/__popc warp aggregation (one atomic per warp,
@@ -231,24 +255,8 @@ __global__ void __launch_bounds__(PTB_SHADE_THREADS, PRIMARY ? PTB_SHADE_MIN_CTA
                 ps.thr = mk(c2.x, c2.y, c2.z), ps.sample = __float_as_uint(c2.w);
                 ps.depth = __float_as_uint(c3.x), ps.rngBlock = __float_as_uint(c3.y);
             }
-            int kind = (int)(h.y >> 16);
             V3 rad = mk(0.f, 0.f, 0.f);
-            if(kind != PTB_HIT_MISS)
-            {
-                uint32_t tag = h.y & 0xFFFFu;
-                Hit hit;
-                hit.t = __uint_as_float(h.x);
-                V3 n = boundaryNormal<false>(sc, tag, hit.t, ps.o, ps.d);
-                hit.mat = __ldg(&sc.primMeta[tag >> 1]).y;
-                if(kind == PTB_HIT_ENTER)
-                    hit.n = n, hit.ior = sc.materials[hit.mat].iorIn; // path-trace.h:72-81
-                else
-                    hit.n = neg(n), hit.ior = sc.materials[hit.mat].ior; // path-trace.h:86-95
-                Philox rng;
-                rngInit(rng, pass.seed, ps.pixel, ps.sample, ps.rngBlock);
-                alive = shadeVertex(sc, ps, hit, rng, pass.flags, rad);
-                ps.rngBlock = rng.block;
-            }
+            alive = shadeHitRecord(sc, pass, ps, h, rad);
             accumulate(accum, ps.pixel, rad, alive ? 0.f : 1.f);
         }
         // survivors go to the warp's staging buffer in shared memory; full groups of 32 are flushed
@@ -292,6 +300,86 @@ __global__ void __launch_bounds__(PTB_SHADE_THREADS, PRIMARY ? PTB_SHADE_MIN_CTA
         if(lane < staged)
             out.q0[slot] = stage[0][lane], out.q1[slot] = stage[1][lane], out.q2[slot] = stage[2][lane], out.q3[slot] = stage[3][lane];
     }
+}
+
+// Tail of a pass (bounce levels that hold a few thousand rays at most): every queued ray is followed to the end
+// of its path inside ONE kernel — trace, shade, trace, ... — instead of a trace / shade launch pair per level on
+// nearly empty queues.  Same device functions, same RNG blocks, hence the same radiance as the level-by-level
+// wavefront (up to the order of the float atomics).  All 32 lanes run the evaluator every trip (its SKIP words and
+// miss exits vote); lanes whose path has ended carry a null ray.  Register-heavy (trace + shade state together),
+// which is why the big levels are NOT run this way.
+template <bool GP>
+__global__ void __launch_bounds__(PTB_FAST_THREADS) tailKernel(DevScene sc, int cap, float *overflow, size_t ovfStride, RenderPass pass, float4 *accum, RayQueue in,
+                                                               const unsigned *__restrict__ inCount, unsigned *extraRays)
+{
+    const unsigned total = *inCount;
+    if(total == 0u)
+        return;
+    FastCtx cx = setupFast<GP, 1>(sc, cap, overflow, ovfStride);
+    const unsigned long long stride = (unsigned long long)gridDim.x * PTB_FAST_THREADS;
+    const unsigned lane = threadIdx.x & 31u;
+    unsigned extra = 0u;
+    for(unsigned long long base = (unsigned long long)blockIdx.x * PTB_FAST_THREADS + (threadIdx.x & ~31u); base < total; base += stride)
+    {
+        const unsigned long long i = base + lane;
+        bool alive = i < total;
+        PathState ps;
+        ps.o = ps.d = ps.thr = mk(0.f, 0.f, 0.f);
+        ps.strength = 0.f, ps.pixel = ps.sample = ps.depth = ps.rngBlock = 0u;
+        if(alive)
+            queueLoad(in, (unsigned)i, ps);
+        bool first = true;
+        while(__any_sync(0xFFFFFFFFu, alive))
+        {
+            V3 o[1] = {alive ? ps.o : mk(0.f, 0.f, 0.f)}, d[1] = {alive ? ps.d : mk(0.f, 0.f, 0.f)};
+            int tops[1];
+            evalFast<GP, false, 1>(cx, sc.fastProgram, o, d, tops);
+            if(alive)
+            {
+                float t = -1.f;
+                uint32_t tag = 0u;
+                const int kind = firstHit(cx.pool, tops[0], t, tag);
+                extra += first ? 0u : 1u;
+                V3 rad = mk(0.f, 0.f, 0.f);
+                alive = shadeHitRecord(sc, pass, ps, make_uint2(__float_as_uint(t), ((uint32_t)kind << 16) | tag), rad);
+                accumulate(accum, ps.pixel, rad, alive ? 0.f : 1.f);
+            }
+            first = false;
+        }
+    }
+#pragma unroll
+    for(int k = 16; k; k >>= 1)
+        extra += __shfl_xor_sync(0xFFFFFFFFu, extra, k);
+    if(lane == 0u && extra)
+        atomicAdd(extraRays, extra);
+}
+void launchTail(const DevScene &sc, const CsgConfig &cfg, int blocks, const RenderPass &pass, float4 *accum, RayQueue in, const unsigned *inCount, unsigned *extraRays, cudaStream_t stream)
+{
+    if(cfg.stageProgram)
+        tailKernel<false><<<blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, pass, accum, in, inCount, extraRays);
+    else
+        tailKernel<true><<<blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, pass, accum, in, inCount, extraRays);
+}
+int tailBlocksPerSm(bool globalProgram, size_t smemBytes)
+{
+    int n = 0;
+    cudaError_t e;
+    if(globalProgram)
+    {
+        cudaFuncSetAttribute(tailKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, tailKernel<true>, PTB_FAST_THREADS, smemBytes);
+    }
+    else
+    {
+        cudaFuncSetAttribute(tailKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, tailKernel<false>, PTB_FAST_THREADS, smemBytes);
+    }
+    if(e != cudaSuccess)
+    {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
 }
 
 void launchTracePrimary(const DevScene &sc, const CsgConfig &cfg, const RenderPass &pass, uint2 *hits, cudaStream_t stream)
@@ -564,6 +652,62 @@ void launchScatterSample(const float *normal, const float *refl, float scatter, 
     int blocks = (int)((n + 127) / 128);
     blocks = blocks < 1 ? 1 : (blocks > 1184 ? 1184 : blocks);
     scatterSampleKernel<<<blocks, 128, 0, stream>>>(mk(normal[0], normal[1], normal[2]), mk(refl[0], refl[1], refl[2]), scatter, n, seed, flags, dirs);
+}
+
+// Vector3D::reflect / refract / refractStrength as the shade kernel computes them (ptb_shade.cuh), for
+// known-answer tests against the reference (include/vector3d.h:186-214).  op 0: reflect -> 3 floats,
+// 1: refract -> 3 floats, 2: refractStrength -> 1 float.
+__global__ void vectorEvalKernel(int op, const float *__restrict__ v, const float *__restrict__ nrm, const float *__restrict__ ior, size_t n, float *__restrict__ out)
+{
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for(size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        const V3 d = mk(v[3 * i], v[3 * i + 1], v[3 * i + 2]), nn = mk(nrm[3 * i], nrm[3 * i + 1], nrm[3 * i + 2]);
+        if(op == 2)
+            out[i] = refractStrength(d, ior[i], nn);
+        else
+        {
+            const V3 r = op == 0 ? vreflect(d, nn) : vrefract(d, ior[i], nn);
+            out[3 * i] = r.x, out[3 * i + 1] = r.y, out[3 * i + 2] = r.z;
+        }
+    }
+}
+void launchVectorEval(int op, const float *v, const float *nrm, const float *ior, size_t n, float *out, cudaStream_t stream)
+{
+    int blocks = (int)((n + 127) / 128);
+    blocks = blocks < 1 ? 1 : (blocks > 1184 ? 1184 : blocks);
+    vectorEvalKernel<<<blocks, 128, 0, stream>>>(op, v, nrm, ior, n, out);
+}
+
+// The random words the render kernels draw, for statistical tests (the reference's LCG,
+// include/path-trace.h:21-54, is replaced by counter-based generators; parity is statistical).
+//   which 0: cameraJitter(seed, pixel, sample)        -> 2 words (sub-pixel x, y)
+//   which 1: Philox block `block` of (pixel, sample)  -> 4 words (shading decisions)
+__global__ void rngWordsKernel(int which, uint64_t seed, const uint32_t *__restrict__ pixel, const uint32_t *__restrict__ sample, const uint32_t *__restrict__ block, size_t n,
+                               uint32_t *__restrict__ out)
+{
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for(size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        if(which == 0)
+        {
+            const uint2 u = cameraJitter(seed, pixel[i], sample[i]);
+            out[2 * i] = u.x, out[2 * i + 1] = u.y;
+        }
+        else
+        {
+            Philox rng;
+            rngInit(rng, seed, pixel[i], sample[i], block ? block[i] : 0u);
+            const uint4 u = rngNext4(rng);
+            out[4 * i] = u.x, out[4 * i + 1] = u.y, out[4 * i + 2] = u.z, out[4 * i + 3] = u.w;
+        }
+    }
+}
+void launchRngWords(int which, uint64_t seed, const uint32_t *pixel, const uint32_t *sample, const uint32_t *block, size_t n, uint32_t *out, cudaStream_t stream)
+{
+    int blocks = (int)((n + 255) / 256);
+    blocks = blocks < 1 ? 1 : (blocks > 1184 ? 1184 : blocks);
+    rngWordsKernel<<<blocks, 256, 0, stream>>>(which, seed, pixel, sample, block, n, out);
 }
 
 // ---- FP32 issue-peak microbenchmark (roofline denominator) -----------------------

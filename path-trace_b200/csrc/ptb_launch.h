@@ -93,6 +93,12 @@ void launchTraceQueue(const DevScene &sc, const CsgConfig &cfg, RayQueue in, con
 void launchShade(const DevScene &sc, int blocks, bool primary, const RenderPass &pass, float4 *accum, const uint2 *hits, RayQueue in, const unsigned *inCount, RayQueue out,
                  unsigned *outCount, cudaStream_t stream);
 int shadeBlocksPerSm(bool primary);
+// Tail of a pass: every ray of `in` (*inCount of them, bounce level >= 2) is followed to the end of its path by
+// ONE kernel — trace, shade, trace, ... in a loop, no queue in between.  *extraRays += rays traced beyond the first
+// of each path.  Uses the trace stage's launch shape (cfg: shared-memory layout of the interpreting evaluator).
+void launchTail(const DevScene &sc, const CsgConfig &cfg, int blocks, const RenderPass &pass, float4 *accum, RayQueue in, const unsigned *inCount, unsigned *extraRays,
+                cudaStream_t stream);
+int tailBlocksPerSm(bool globalProgram, size_t smemBytes);
 void launchResolve(const float4 *accum, float4 *rgba, size_t nPixels, cudaStream_t stream);
 void launchDisplay8(const float4 *rgba, uchar4 *out, size_t nPixels, bool divideByAlpha, cudaStream_t stream);
 
@@ -123,6 +129,8 @@ void launchAdaptiveResolveList(const float4 *accum, float4 *value, const uint32_
 void launchAdaptiveAssemble(const float4 *value, const float4 *interp, int pitch, int width, int height, float4 *rgba, uint8_t *source, cudaStream_t stream);
 void launchTextureEval(const DevScene &sc, int root, const float *pos, size_t n, float *rgb, float *f, uint32_t flags, cudaStream_t stream);
 void launchScatterSample(const float *normal, const float *refl, float scatter, size_t n, uint64_t seed, uint32_t flags, float *dirs, cudaStream_t stream);
+void launchVectorEval(int op, const float *v, const float *nrm, const float *ior, size_t n, float *out, cudaStream_t stream);
+void launchRngWords(int which, uint64_t seed, const uint32_t *pixel, const uint32_t *sample, const uint32_t *block, size_t n, uint32_t *out, cudaStream_t stream);
 // FMA-chain microbenchmark: returns lane-FMAs executed.
 double launchFmaPeak(int blocks, int threads, int iters, cudaStream_t stream);
 size_t csgSharedBytes(const DevScene &sc, int threads, int cap, bool stageProgram);

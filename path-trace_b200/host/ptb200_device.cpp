@@ -60,6 +60,36 @@ void renderFrameAdaptive(const DeviceScene &scene, const PtbRenderParams &params
     check(ptb200_render_adaptive(scene.handle(), &params, &adaptive, rgba, NULL, NULL, stats, adaptiveStats));
 }
 
+MultiDeviceScene::MultiDeviceScene(const PathTrace::Object *world, const std::vector<int> &devices) : comm(NULL)
+{
+    std::vector<int> devs = devices;
+    if(devs.empty())
+        for(int i = 0; i < ptb200_device_count(); i++)
+            devs.push_back(i);
+    Flattener f;
+    world->flatten(f);
+    PtbSceneDesc d = f.desc();
+    check(ptb200_comm_init_all(devs.data(), (int)devs.size(), &comm));
+    scenes.assign(devs.size(), (PtbScene *)NULL);
+    int rc = ptb200_scene_create_multi(comm, &d, scenes.data());
+    if(rc != 0)
+    {
+        std::string msg = ptb200_last_error();
+        ptb200_comm_destroy(comm);
+        throw DeviceError(rc, msg);
+    }
+}
+MultiDeviceScene::~MultiDeviceScene()
+{
+    for(size_t i = 0; i < scenes.size(); i++)
+        ptb200_scene_destroy(scenes[i]);
+    ptb200_comm_destroy(comm);
+}
+void MultiDeviceScene::render(const PtbRenderParams &params, float *rgba, PtbStats *statsPerDevice)
+{
+    check(ptb200_render_multi(comm, scenes.data(), &params, rgba, NULL, statsPerDevice, NULL));
+}
+
 GpuBlockRenderer::GpuBlockRenderer(const DeviceScene &scene, int x, int y, int size, const PtbRenderParams &frame) : job(NULL)
 {
     PtbRenderParams p = frame;

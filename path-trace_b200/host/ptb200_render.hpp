@@ -47,6 +47,25 @@ PtbAdaptiveParams adaptiveDefaults(int width, int height);
 void renderFrameAdaptive(const DeviceScene &scene, const PtbRenderParams &params, const PtbAdaptiveParams &adaptive, float *rgba, PtbStats *stats = NULL,
                          PtbAdaptiveStats *adaptiveStats = NULL);
 
+// One process driving several GPUs (ptb200_comm_init_all): the scene replicated on every device (image
+// pixels cross PCIe once, NCCL broadcast to the others), frames rendered sample-sharded with one NCCL
+// reduce-scatter, every device delivering its own rows of `rgba`.  The counterpart of the reference's render
+// farm client loop (src/test.cpp:520-630), without the sockets.
+class MultiDeviceScene
+{
+public:
+    MultiDeviceScene(const PathTrace::Object *world, const std::vector<int> &devices); // devices empty: all of them
+    ~MultiDeviceScene();
+    int deviceCount() const { return (int)scenes.size(); }
+    void render(const PtbRenderParams &params, float *rgba, PtbStats *statsPerDevice = NULL);
+
+private:
+    PtbComm *comm;
+    std::vector<PtbScene *> scenes;
+    MultiDeviceScene(const MultiDeviceScene &);
+    MultiDeviceScene &operator=(const MultiDeviceScene &);
+};
+
 // Drop-in for the reference's BlockRenderer (src/test.cpp:310-323): construction starts the
 // work asynchronously, done() polls, copyToBuffer() may be called repeatedly while it runs and
 // writes only pixels that already have a value.

@@ -20,6 +20,7 @@ PTB_FLAG_ORIGIN0 = 8
 PTB_FLAG_SPECIALIZE = 16
 PTB_FLAG_INTERPRET = 32
 PTB_HIT_MISS, PTB_HIT_ENTER, PTB_HIT_EXIT = 0, 1, 2
+PTB_COMM_ID_BYTES = 128
 
 
 class PtbPrim(C.Structure):
@@ -72,6 +73,7 @@ class PtbStats(C.Structure):
         ("paths", C.c_uint64), ("rays", C.c_uint64), ("launches", C.c_uint64), ("queue_bytes", C.c_uint64),
         ("ms_total", C.c_float), ("ms_primary", C.c_float), ("ms_bounce", C.c_float), ("ms_resolve", C.c_float),
         ("rays_primary", C.c_uint64), ("rays_bounce", C.c_uint64), ("ms_trace_primary", C.c_float), ("ms_trace_bounce", C.c_float),
+        ("rays_first_bounce", C.c_uint64), ("launches_elided", C.c_uint64), ("ms_shade_primary", C.c_float), ("ms_shade_bounce", C.c_float),
     ]
 
     def as_dict(self):
@@ -97,6 +99,8 @@ ABI_SYMBOLS = [
     "ptb200_last_error", "ptb200_abi_version", "ptb200_device_count", "ptb200_trim", "ptb200_scene_create", "ptb200_scene_destroy", "ptb200_image_upload",
     "ptb200_intersect", "ptb200_intersect_device", "ptb200_texture_eval", "ptb200_render", "ptb200_render_adaptive", "ptb200_render_accumulate_device", "ptb200_resolve_device", "ptb200_display8_device", "ptb200_display8",
     "ptb200_render_async", "ptb200_job_done", "ptb200_job_read", "ptb200_job_wait", "ptb200_job_destroy", "ptb200_sample_scatter", "ptb200_fp32_peak", "ptb200_specialize_probe", "ptb200_scene_specialized", "ptb200_tile_request_parse", "ptb200_tile_encode", "ptb200_tile_decode",
+    "ptb200_comm_unique_id", "ptb200_comm_init_rank", "ptb200_comm_init_all", "ptb200_comm_info", "ptb200_comm_destroy", "ptb200_scene_create_multi", "ptb200_render_multi",
+    "ptb200_multi_rows", "ptb200_multi_shard", "ptb200_vector_eval", "ptb200_rng_words",
 ]
 
 _vp, _f, _i, _sz = C.c_void_p, C.c_float, C.c_int, C.c_size_t
@@ -206,6 +210,19 @@ def product():
         lib.ptb200_tile_encode.argtypes = [_vp, _i, _i, _i, _i, _i, _vp, _i, C.c_char_p, _sz, C.POINTER(_sz)]
         lib.ptb200_tile_decode.argtypes = [C.c_char_p, _sz, _i, _i, _i, _vp, _vp, C.POINTER(_i), C.POINTER(_sz)]
         lib.ptb200_fp32_peak.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        _ip = C.POINTER(_i)
+        lib.ptb200_vector_eval.argtypes = [_i, _vp, _vp, _vp, _sz, _vp]
+        lib.ptb200_rng_words.argtypes = [_i, C.c_uint64, _vp, _vp, _vp, _sz, _vp]
+        lib.ptb200_comm_unique_id.argtypes = [_vp]
+        lib.ptb200_comm_init_rank.argtypes = [C.c_char_p, _i, _i, C.POINTER(_vp)]
+        lib.ptb200_comm_init_all.argtypes = [_ip, _i, C.POINTER(_vp)]
+        lib.ptb200_comm_info.argtypes = [_vp, _ip, _ip, _ip]
+        lib.ptb200_comm_destroy.argtypes = [_vp]
+        lib.ptb200_comm_destroy.restype = None
+        lib.ptb200_scene_create_multi.argtypes = [_vp, C.POINTER(PtbSceneDesc), C.POINTER(_vp)]
+        lib.ptb200_render_multi.argtypes = [_vp, C.POINTER(_vp), C.POINTER(PtbRenderParams), _vp, C.POINTER(_vp), C.POINTER(PtbStats), _vp]
+        lib.ptb200_multi_rows.argtypes = [_i, _i, _i, _ip, _ip]
+        lib.ptb200_multi_shard.argtypes = [_i, _i, _i, _ip, _ip, _ip]
         bind_builder(lib, "ptbh_")
         lib.ptbh_flatten.restype = _vp
         lib.ptbh_flatten.argtypes = [_vp]

@@ -1,8 +1,10 @@
-"""Host-side logic of the sample-sharded multi-GPU path (ptb200/multi.py) on CPU: gloo backend,
-world size 2 (and 3, ragged).  The device calls are replaced by a deterministic stand-in that adds
-f(pixel, global sample index) for every sample of the shard — what matters here is that the shards
-partition the sample set, that one sum-reduce + resolve reproduces the unsharded frame, and that only
-rank 0 resolves."""
+"""Host-side logic of the sample-sharded multi-GPU path on CPU: gloo backend, world size 2 (and 3,
+ragged).  The partition rules are the library's own pure functions (ptb200_multi_shard / ptb200_multi_rows,
+csrc/ptb_multi.cu — the ones ptb200_render_multi uses); the device calls are replaced by a deterministic
+stand-in that adds f(pixel, global sample index) for every sample of the shard, and the NCCL reduce-scatter by
+an all-reduce + slice (gloo has none).  What matters here: the shards partition the sample set, the row blocks
+partition the frame, summing the shards and resolving row blocks per rank reproduces the unsharded frame, and
+the 128-byte communicator id travels from rank 0 to every rank."""
 import os
 import socket
 
@@ -32,6 +34,25 @@ def test_shards_partition_the_sample_set():
         multi.shard_samples(-1, 0, 2)
 
 
+def test_row_blocks_partition_the_frame():
+    for height in (1, 2, 9, 54, 1080, 2160):
+        for world in (1, 2, 3, 4, 8):
+            rows, sizes = [], set()
+            for rank in range(world):
+                r0, r1 = multi.rows_of(height, rank, world)
+                assert 0 <= r0 <= r1 <= height
+                rows += list(range(r0, r1))
+                if r1 - r0:
+                    sizes.add(r1 - r0)
+            assert rows == list(range(height)), (height, world)
+            block = -(-height // world)
+            assert max(sizes) == min(block, height)  # equal blocks (reduce-scatter), the last ones ragged or empty
+    with pytest.raises(ValueError):
+        multi.rows_of(0, 0, 2)
+    with pytest.raises(ValueError):
+        multi.rows_of(8, 2, 2)
+
+
 def contribution(sample):
     """Radiance the stand-in renderer adds to every pixel for one global sample index."""
     pix = torch.arange(W * H, dtype=torch.float32).reshape(H, W)
@@ -59,10 +80,11 @@ def worker(rank, world, port, spp, results):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
+        ident = multi.exchange_id(dist, lambda: bytes(range(128)))
         accum = torch.zeros(H, W, 4)
         out = torch.full((H, W, 4), -1.0)
-        stats = multi.render_sharded(fake_render_accumulate, fake_resolve, make_params, spp, accum, out, dist)
-        results[rank] = (out.numpy().copy(), stats)
+        stats = multi.render_rows_emulated(fake_render_accumulate, fake_resolve, make_params, spp, accum, out, dist)
+        results[rank] = (out.numpy().copy(), stats, ident)
     finally:
         dist.destroy_process_group()
 
@@ -85,10 +107,13 @@ def test_sharded_frame_equals_unsharded(world, spp):
     fake_render_accumulate(dict(spp=spp, sample_offset=0, sample_stride=1), accum)
     want = torch.empty(H, W, 4)
     fake_resolve(accum, want)
-    out0, _ = results[0]
-    assert np.allclose(out0, want.numpy(), rtol=1e-6, atol=1e-6)
-    for rank in range(1, world):
-        out, stats = results[rank]
-        assert (out == -1.0).all()  # only rank 0 resolves
+    frame = np.full((H, W, 4), -1.0, np.float32)
+    for rank in range(world):
+        out, stats, ident = results[rank]
+        assert ident == bytes(range(128))  # every rank got rank 0's communicator id
+        r0, r1 = multi.rows_of(H, rank, world)
+        assert (out[:r0] == -1.0).all() and (out[r1:] == -1.0).all()  # a rank delivers its own rows only
+        frame[r0:r1] = out[r0:r1]
         count, _, _ = multi.shard_samples(spp, rank, world)
         assert stats == (count if count else None)
+    assert np.allclose(frame, want.numpy(), rtol=1e-6, atol=1e-6)
