@@ -256,6 +256,11 @@ int ptb200_texture_eval(PtbScene *scene, int tex_root, const float *positions, s
 /* Synchronous frame render.  rgba_out: host, width*height*4 floats, mean radiance over spp in
  * rgb and 1 in alpha (pixels outside the rectangle are left untouched). */
 int ptb200_render(PtbScene *scene, const PtbRenderParams *params, float *rgba_out, PtbStats *stats);
+/* tracePixel for a list of n pixels (xy: n pairs x, y): rgba_out gets n x 4 floats, mean radiance over spp and
+ * alpha 1.  Each pixel has the value a frame render with the same params gives it (same samples, same RNG
+ * streams); params->x0..y1 are ignored.  The reference calls tracePixel per pixel (include/path-trace.h:187-207,
+ * src/test.cpp:450); this is that call for a batch. */
+int ptb200_render_pixels(PtbScene *scene, const PtbRenderParams *params, const int32_t *xy, size_t n, float *rgba_out, PtbStats *stats);
 /* Adds this call's UNNORMALISED radiance sums (rgb) and completed-sample counts (alpha) into a
  * device buffer of width*height float4.  Used for sample-sharded multi-GPU rendering: every rank
  * accumulates its slice, one NCCL sum-reduce follows, ptb200_resolve_device divides.  Synchronous

@@ -1225,10 +1225,11 @@ extern "C" int ptb200_scene_specialized(PtbScene *s, double *compile_ms, int *pa
         *passes_specialized = s->lastSpecPasses;
     if(passes_total)
         *passes_total = s->lastPasses;
-    if(s->specSource[SPEC_TRACE].empty())
+    const int which = s->specSource[SPEC_TRACE].empty() ? SPEC_INTERSECT : SPEC_TRACE; // a scene only used for ray batches has the ray-batch kernels
+    if(s->specSource[which].empty())
         return 0;
     std::string err;
-    const SpecKernels *k = specializeGet(s->specSource[SPEC_TRACE], s->device, SPEC_PEEK, err);
+    const SpecKernels *k = specializeGet(s->specSource[which], s->device, SPEC_PEEK, err);
     if(k && compile_ms)
         *compile_ms = k->compileMs;
     return k ? 1 : 0;
@@ -1436,7 +1437,7 @@ int ptb::renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbS
     // loop, no queue).  PTB_TAIL_LEVEL: first bounce level the tail kernel owns (0 = off: a pair per level).
     static const int tailEnv = [] {
         const char *e = getenv("PTB_TAIL_LEVEL");
-        return e ? atoi(e) : 3;
+        return e ? atoi(e) : 4; // measured on C5 (865 ms frames): pairs only 853, tail from level 2: 909, 3: 865, 4: 845
     }();
     const int tailLevel = tailEnv > 0 && tailEnv <= p->max_depth && tailBlocksPerSm(!cfg.stageProgram, cfg.smemBytes) > 0 ? tailEnv : p->max_depth + 1;
     const int pairLevels = std::min(p->max_depth, tailLevel - 1); // bounce levels run as trace + shade pairs
@@ -1652,6 +1653,54 @@ extern "C" int ptb200_render(PtbScene *s, const PtbRenderParams *p, float *rgba_
         stats->ms_resolve = ms;
         stats->launches += 1;
     }
+    return PTB_OK;
+}
+
+// tracePixel for a LIST of pixels (reference include/path-trace.h:187-207, called per pixel at src/test.cpp:450):
+// the wavefront runs over the listed pixels only; every pixel gets the samples, RNG streams and hence the value it
+// has in a frame render with the same parameters.
+extern "C" int ptb200_render_pixels(PtbScene *s, const PtbRenderParams *p, const int32_t *xy, size_t n, float *rgba_out, PtbStats *stats)
+{
+    if(!s || (n && (!xy || !rgba_out)))
+        return fail(PTB_EINVAL, "null argument");
+    int x0, y0, rw, rh;
+    if(int rc = checkParams(p, x0, y0, rw, rh))
+        return rc;
+    if(p->width > 65535 || p->height > 65535 || n > 0x7FFFFFFFull)
+        return fail(PTB_EINVAL, "image or list too large for a pixel list (16-bit coordinates)");
+    if(stats)
+        memset(stats, 0, sizeof(*stats));
+    if(n == 0)
+        return PTB_OK;
+    std::vector<uint32_t> packed(n);
+    for(size_t i = 0; i < n; i++)
+    {
+        const int x = xy[2 * i], y = xy[2 * i + 1];
+        if(x < 0 || y < 0 || x >= p->width || y >= p->height)
+            return fail(PTB_EINVAL, "listed pixel outside the image");
+        packed[i] = ((uint32_t)y << 16) | (uint32_t)x;
+    }
+    std::lock_guard<std::mutex> g(s->lock);
+    if(s->asyncBusy)
+        return fail(PTB_EBUSY, "an asynchronous render is running on this scene");
+    CU(cudaSetDevice(s->device));
+    const size_t nPix = (size_t)p->width * p->height;
+    CU(ensureScratch(s, s->scratch.accum, nPix * 16));
+    DeviceBuffer list, out;
+    CU(list.ensure(n * 4));
+    CU(out.ensure(n * 16));
+    float4 *accum = (float4 *)s->scratch.accum.p;
+    CU(cudaMemcpy(list.p, packed.data(), n * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemsetAsync(accum, 0, nPix * 16, nullptr));
+    PixelListArg arg{(const uint32_t *)list.p, (unsigned)n, p->width};
+    PtbStats local;
+    if(int rc = renderPasses(s, p, accum, stats ? stats : &local, nullptr, &arg))
+        return rc;
+    launchGatherPixels(accum, (const uint32_t *)list.p, (unsigned)n, p->width, (float4 *)out.p, nullptr);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(rgba_out, out.p, n * 16, cudaMemcpyDeviceToHost));
+    if(stats)
+        stats->launches += 1;
     return PTB_OK;
 }
 

@@ -586,6 +586,26 @@ void launchAdaptiveResolveList(const float4 *accum, float4 *value, const uint32_
     adaptiveResolveListKernel<<<blocks > 148 * 8 ? 148 * 8 : blocks, 256, 0, stream>>>(accum, value, pixelList, n, pitch);
 }
 
+// out[i] = mean radiance of listed pixel i (y << 16 | x) of an accumulation frame
+__global__ void gatherPixelsKernel(const float4 *__restrict__ accum, const uint32_t *__restrict__ pixelList, unsigned n, int pitch, float4 *__restrict__ out)
+{
+    const unsigned stride = gridDim.x * blockDim.x;
+    for(unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        const uint32_t packed = pixelList[i];
+        const float4 a = accum[(size_t)(packed >> 16) * pitch + (packed & 0xFFFFu)];
+        const float inv = a.w > 0.f ? 1.f / a.w : 0.f;
+        out[i] = make_float4(a.x * inv, a.y * inv, a.z * inv, a.w > 0.f ? 1.f : 0.f);
+    }
+}
+void launchGatherPixels(const float4 *accum, const uint32_t *pixelList, unsigned n, int pitch, float4 *out, cudaStream_t stream)
+{
+    if(n == 0u)
+        return;
+    int blocks = (int)((n + 255u) / 256u);
+    gatherPixelsKernel<<<blocks > 148 * 8 ? 148 * 8 : blocks, 256, 0, stream>>>(accum, pixelList, n, pitch, out);
+}
+
 __global__ void adaptiveAssembleKernel(const float4 *__restrict__ value, const float4 *__restrict__ interp, int pitch, int width, int height, float4 *__restrict__ rgba,
                                        uint8_t *__restrict__ source)
 {

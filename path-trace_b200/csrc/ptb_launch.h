@@ -127,6 +127,7 @@ size_t adaptiveSortList(uint32_t *list, uint32_t *alt, unsigned n, void *temp, s
 void launchAdaptiveResolveList(const float4 *accum, float4 *value, const uint32_t *pixelList, unsigned n, int pitch, cudaStream_t stream);
 // rgba (width x height) = interpolated pixel where there is one, else the traced one; source: 1 traced, 2 interpolated
 void launchAdaptiveAssemble(const float4 *value, const float4 *interp, int pitch, int width, int height, float4 *rgba, uint8_t *source, cudaStream_t stream);
+void launchGatherPixels(const float4 *accum, const uint32_t *pixelList, unsigned n, int pitch, float4 *out, cudaStream_t stream);
 void launchTextureEval(const DevScene &sc, int root, const float *pos, size_t n, float *rgb, float *f, uint32_t flags, cudaStream_t stream);
 void launchScatterSample(const float *normal, const float *refl, float scatter, size_t n, uint64_t seed, uint32_t flags, float *dirs, cudaStream_t stream);
 void launchVectorEval(int op, const float *v, const float *nrm, const float *ior, size_t n, float *out, cudaStream_t stream);

@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <string>
+#include <vector>
 
 #include "ptb200.h"
 
@@ -30,6 +31,7 @@ extern "C" int ptb200_tile_encode(const float *rgba, int width, int height, int 
     if(!rgba || width <= 0 || height <= 0 || size <= 0 || !length)
         return PTB_EINVAL;
     std::string s;
+    std::vector<uint8_t *> marked; // wrotePixel flags of the pixels in the text: committed only once the text is in `out`
     char buf[128];
     for(int py = y; py < y + size; py++) // RenderBlock::copyToSocket, src/test.cpp:374-388
         for(int px = x; px < x + size; px++)
@@ -41,7 +43,7 @@ extern "C" int ptb200_tile_encode(const float *rgba, int width, int height, int 
             if(!(p[3] > 0.f) || (flag && *flag))
                 continue; // validPixel && !wrotePixel
             if(flag)
-                *flag = 1;
+                marked.push_back(flag);
             snprintf(buf, sizeof(buf), "P%i,%i=%g,%g,%g\n", px, py, p[0], p[1], p[2]);
             s += buf;
         }
@@ -49,12 +51,13 @@ extern "C" int ptb200_tile_encode(const float *rgba, int width, int height, int 
     if(final)
         s += "F\n"; // src/test.cpp:715
     *length = s.size();
-    if(out && capacity)
-    {
-        if(capacity < s.size() + 1)
-            return PTB_ENOMEM;
-        memcpy(out, s.c_str(), s.size() + 1);
-    }
+    if(!out || !capacity)
+        return PTB_OK; // measuring only: sent[] is untouched, the next call sends the same pixels
+    if(capacity < s.size() + 1)
+        return PTB_ENOMEM; // nothing was sent
+    memcpy(out, s.c_str(), s.size() + 1);
+    for(uint8_t *flag : marked)
+        *flag = 1;
     return PTB_OK;
 }
 

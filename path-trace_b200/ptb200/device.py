@@ -104,6 +104,14 @@ class DeviceScene:
         check(capi.product().ptb200_render(self.handle, C.byref(params), out.ctypes.data, C.byref(stats)))
         return out, stats
 
+    def render_pixels(self, params, xy):
+        """ptb200_render_pixels: the listed pixels (n x 2 ints: x, y) only -> (n, 4) float32, stats."""
+        xy = np.ascontiguousarray(xy, dtype=np.int32).reshape(-1, 2)
+        out = np.zeros((len(xy), 4), np.float32)
+        stats = PtbStats()
+        check(capi.product().ptb200_render_pixels(self.handle, C.byref(params), xy.ctypes.data, len(xy), out.ctypes.data, C.byref(stats)))
+        return out, stats
+
     def render_adaptive(self, params, block_size=32, max_sample_size=None, min_color_delta=0.003, want_lattice=True):
         """ptb200_render_adaptive: the reference's pixel-skipping quadtree (src/test.cpp:423-499).
         Defaults are the reference's constants (src/test.cpp:38,50).  Returns image, source map

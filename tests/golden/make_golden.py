@@ -43,12 +43,14 @@ def main():
     out["c3_spans"], out["c3_counts"] = spans, counts
     np.savez_compressed(os.path.join(OUT, "spans.npz"), **out)
 
-    # 2. seeded renders of the image configs on a lattice of the 1920x1080 image plane
+    # 2. seeded renders of the image configs on a lattice of their image plane (gc.RENDER_SETUP: c1/c2 1920x1080,
+    #    c4/c5 3840x2160 with the full-size assets bench.py times)
     out = {}
     for name in gc.RENDER_CASES:
         rb.materials_reset()
         world = gc.render_scene(rb, name)
-        rgb, info = common.ref_render_mt(lib, world, *gc.LATTICE, gc.RENDER_SPP, 16, gc.RENDER_SEED, os.cpu_count())
+        lattice, ref_spp, _ = gc.RENDER_SETUP[name]
+        rgb, info = common.ref_render_mt(lib, world, *lattice, ref_spp, 16, gc.RENDER_SEED, os.cpu_count())
         out[name] = rgb
         out[name + "_rays"] = np.array([info["rays"]], np.uint64)
         print(name, "mean", rgb.mean(), "rays", info["rays"], "%.1fs" % info["seconds"])
@@ -75,6 +77,23 @@ def main():
     for k, m in mats.items():
         out["mat_" + k] = np.array(m, np.float32)
     np.savez_compressed(os.path.join(OUT, "kat.npz"), **out)
+    # 4. the reference's tile renderer and tile wire text (oracle/_ref/libptref_block.so) on the seeded lattice of
+    #    tests/block_cases.py: digests of whole rows of tiles, and the socket text + screen pixels of two tiles
+    import block_cases as bc
+    blib = bc.block_lib()
+    lat = bc.lattice()
+    rgb, missing = bc.ref_frame(blib, lat)
+    assert missing == 0
+    out = {}
+    for tr in bc.TILE_ROWS:
+        y0 = tr * bc.BLOCK
+        out["frame_rows_sha256_%d" % tr] = np.array(bc.digest(rgb[y0:min(bc.H, y0 + bc.BLOCK)]))
+    for k, (x, y) in enumerate(bc.TEXT_TILES):
+        first, _ = bc.ref_socket_text(blib, lat, x, y)
+        out["tile_text_%d" % k] = np.frombuffer(first.encode(), np.uint8)
+        tile = rgb[y:y + bc.BLOCK, x:x + bc.BLOCK]
+        out["tile_rgba_%d" % k] = np.concatenate([tile, np.ones(tile.shape[:2] + (1,), np.float32)], 2)
+    np.savez_compressed(os.path.join(OUT, "blocks.npz"), **out)
     print("golden vectors written to", OUT)
 
 

@@ -14,9 +14,20 @@ TRACE_SEED = 4242
 C3_RAYS = 4000
 # every 20th pixel of the 1920x1080 image plane: the author's own 96x54-ish preview scale
 LATTICE = (1920, 1080, 10, 10, 20, 96, 54)
+# configs 4 and 5 are 3840x2160 (BASELINE.json): every 40th pixel of THAT image plane, camera of src/test.cpp:450 at 4K
+LATTICE_4K = (3840, 2160, 20, 20, 40, 96, 54)
 RENDER_SPP = 8
 RENDER_SEED = 20260401
 RENDER_CASES = ["c1", "c2", "c4", "c5"]
+# per case: (lattice, reference camera samples per pixel, GPU samples per pixel).  A reference camera sample carries
+# ~10^4 scatter rays, a GPU sample one: c5's diffuse surfaces see a 1.5-degree sun (3.4e-4 of the hemisphere), so it
+# takes 64 reference samples (~220 sun hits per pixel) and 2^16 GPU samples for both sides' noise to fall to ~3 %.
+RENDER_SETUP = {
+    "c1": (LATTICE, 8, 4096),
+    "c2": (LATTICE, 8, 4096),
+    "c4": (LATTICE_4K, 16, 16384),
+    "c5": (LATTICE_4K, 64, 65536),
+}
 KAT_N = 512
 KAT_SEED = 977
 
@@ -38,15 +49,17 @@ def small_env():
     return scenes.env_latlong(800, 400)
 
 
-def render_scene(b, name):
+def render_scene(b, name, small=False):
+    """The scene of an image config.  c4 / c5 with the FULL-SIZE assets bench.py times (640x480 and 1280x1509
+    textures, 3200x1600 environment) unless small (quick property tests that do not compare with a golden)."""
     if name == "c1":
         return scenes.config1(b, env=small_env())
     if name == "c2":
         return scenes.config2(b)
     if name == "c4":
-        return scenes.config4(b, images=small_images())
+        return scenes.config4(b, images=small_images()) if small else scenes.config4(b)
     if name == "c5":
-        return scenes.config5(b, env=small_env(), images=small_images())
+        return scenes.config5(b, env=small_env(), images=small_images()) if small else scenes.config5(b)
     raise KeyError(name)
 
 

@@ -75,7 +75,7 @@ def test_config3_batch_exact_and_fast():
 @pytest.mark.parametrize("name", ["c1", "c2", "c4", "c5"])
 def test_camera_rays_on_image_configs(name):
     b = product_builder()
-    flat = device.Flat(gc.render_scene(b, name))
+    flat = device.Flat(gc.render_scene(b, name, small=True))  # geometry only: the small stand-in images
     sc = device.DeviceScene(flat)
     rs = np.random.RandomState(8)
     n = 60000
@@ -93,7 +93,7 @@ def test_camera_rays_on_image_configs(name):
 def test_pool_overflow_path_matches(monkeypatch):
     """Force a tiny shared-memory pool so lists spill to the global overflow area."""
     b = product_builder()
-    flat = device.Flat(gc.render_scene(b, "c4"))
+    flat = device.Flat(gc.render_scene(b, "c4", small=True))
     sc = device.DeviceScene(flat)
     rs = np.random.RandomState(9)
     n = 20000

@@ -22,8 +22,7 @@ RENDERS = np.load(os.path.join(common.GOLDEN, "renders.npz"))
 
 # Tolerances (relative to the golden image's mean radiance):
 MEAN_TOL = 0.005      # |mean(gpu) - mean(ref)| / mean(ref)
-RMSE_TOL = {"c1": 0.04, "c2": 0.015, "c4": 0.025, "c5": 0.2}  # per-pixel RMS error / mean(ref); c5 is lit by a 1.5-degree sun, both sides are noisy there
-GPU_SPP = 4096
+RMSE_TOL = {"c1": 0.04, "c2": 0.015, "c4": 0.025, "c5": 0.05}  # per-pixel RMS error / mean(ref); sample counts per case: golden_cases.RENDER_SETUP
 
 
 def test_texture_known_answers():
@@ -95,27 +94,39 @@ def test_scatter_lobe_rotated_frame():
     assert (got @ normal).min() > 0
 
 
-def render_on_lattice(sc, spp, seed=1, flags=0):
-    """The golden lattice is every 20th pixel of 1920x1080: render those pixels only, as tiny
-    rectangles of the full-size image plane."""
-    W, H, x0, y0, step, nx, ny = gc.LATTICE
-    out = np.zeros((ny, nx, 3), np.float32)
-    frame = np.zeros((H, W, 4), np.float32)
-    stats = None
-    for j in range(ny):
-        p = device.default_params(W, H, spp, seed=seed, flags=flags, rect=(x0, y0 + j * step, x0 + (nx - 1) * step + 1, y0 + j * step + 1))
-        _, stats = sc.render(p, frame)
-        out[j] = frame[y0 + j * step, x0:x0 + (nx - 1) * step + 1:step, :3]
-    return out, stats
+def render_on_lattice(sc, spp, seed=1, flags=0, lattice=None):
+    """The golden lattice is every 20th (40th at 4K) pixel of the image plane: ptb200_render_pixels traces
+    exactly those pixels of the full-size frame."""
+    W, H, x0, y0, step, nx, ny = lattice or gc.LATTICE
+    ys, xs = np.meshgrid(y0 + step * np.arange(ny), x0 + step * np.arange(nx), indexing="ij")
+    out, stats = sc.render_pixels(device.default_params(W, H, spp, seed=seed, flags=flags), np.stack([xs.ravel(), ys.ravel()], 1))
+    assert (out[:, 3] == 1).all()
+    return out[:, :3].reshape(ny, nx, 3), stats
+
+
+def test_render_pixels_equals_the_frame_render():
+    """A listed pixel has the value the frame render gives it (same samples, same RNG streams)."""
+    sc = device.DeviceScene(device.Flat(gc.render_scene(product_builder(), "c2")))
+    W, H = 192, 108
+    p = device.default_params(W, H, 64, seed=5)
+    frame, st = sc.render(p)
+    rs = np.random.RandomState(1)
+    xy = np.stack([rs.randint(0, W, 500), rs.randint(0, H, 500)], 1)
+    got, st2 = sc.render_pixels(p, xy)
+    assert np.allclose(got, frame[xy[:, 1], xy[:, 0]], rtol=1e-5, atol=1e-6)
+    assert st2.paths == 500 * 64
+    with pytest.raises(capi.PtbError):
+        sc.render_pixels(p, [[W, 0]])
 
 
 @pytest.mark.parametrize("name", gc.RENDER_CASES)
 def test_image_matches_reference_golden(name):
     b = product_builder()
-    flat = device.Flat(gc.render_scene(b, name))
+    flat = device.Flat(gc.render_scene(b, name))  # c4 / c5: the full-size assets and the 4K camera bench.py times
     sc = device.DeviceScene(flat)
     gold = RENDERS[name]
-    img, _ = render_on_lattice(sc, GPU_SPP)
+    lattice, _, gpu_spp = gc.RENDER_SETUP[name]
+    img, _ = render_on_lattice(sc, gpu_spp, lattice=lattice)
     mean = gold.mean()
     rel_mean = abs(img.mean() - mean) / mean
     rmse = np.sqrt(((img - gold) ** 2).mean()) / mean

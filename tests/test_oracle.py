@@ -65,9 +65,9 @@ def test_render_rows_match_reference_golden(name):
     b = product_builder()
     b.materials_reset()
     flat = device.Flat(gc.render_scene(b, name))
-    W, H, x0, y0, step, nx, ny = gc.LATTICE
-    rows = 2
-    rgb, info = common.orc_render_mt(flat, W, H, x0, y0, step, nx, rows, gc.RENDER_SPP, 16, gc.RENDER_SEED, 2)
+    (W, H, x0, y0, step, nx, ny), ref_spp, _ = gc.RENDER_SETUP[name]
+    rows = 2 if name == "c1" else 1
+    rgb, info = common.orc_render_mt(flat, W, H, x0, y0, step, nx, rows, ref_spp, 16, gc.RENDER_SEED, 2)
     assert same_bits(rgb, RENDERS[name][:rows])
 
 

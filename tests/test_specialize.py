@@ -82,7 +82,7 @@ def test_specialised_kernels_with_span_pool_overflow(monkeypatch):
     """A two-slot shared-memory pool: span lists of the specialised kernels spill to the global overflow
     area (SpecShared.ovf) and still equal the interpreter's with its default pool."""
     b = product_builder()
-    scene = device.DeviceScene(device.Flat(gc.render_scene(b, "c4")))
+    scene = device.DeviceScene(device.Flat(gc.render_scene(b, "c4", small=True)))
     rs = np.random.RandomState(9)
     n = 20000
     o = rs.uniform(-3, 3, (n, 3)).astype(np.float32) + np.array([0, 0, -9.0], np.float32)

@@ -14,8 +14,10 @@ def encode(frame, x, y, size, sent=None, final=False):
     sp = sent.ctypes.data if sent is not None else None
     before = sent.copy() if sent is not None else None
     assert lib.ptb200_tile_encode(frame.ctypes.data, w, h, x, y, size, sp, int(final), None, 0, C.byref(n)) == 0
-    if sent is not None:
-        sent[:] = before  # measuring marks pixels too: undo
+    tiny = C.create_string_buffer(2)
+    if n.value + 1 > 2:  # a buffer that is too small: PTB_ENOMEM, and nothing counts as sent
+        assert lib.ptb200_tile_encode(frame.ctypes.data, w, h, x, y, size, sp, int(final), tiny, 2, C.byref(n)) == -3
+    assert sent is None or (sent == before).all()  # measuring (out == NULL) and failing leave sent[] alone
     buf = C.create_string_buffer(n.value + 1)
     assert lib.ptb200_tile_encode(frame.ctypes.data, w, h, x, y, size, sp, int(final), buf, len(buf), C.byref(n)) == 0
     return buf.value.decode()
