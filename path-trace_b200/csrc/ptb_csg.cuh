@@ -171,7 +171,8 @@ struct MergeCursor
     int a, aEnd, b, bEnd, out;
     SpanRec spanA, spanB;
     bool aEnded, bEnded;
-    __device__ __forceinline__ MergeCursor(const P &pool, int a0, int b0, int top, int dst) : pool(pool), a(a0), aEnd(b0), b(b0), bEnd(top), out(dst), aEnded(false), bEnded(false)
+    // A = pool slots [a0, aEnd), B = [b0, bEnd); output from slot dst on
+    __device__ __forceinline__ MergeCursor(const P &pool, int a0, int aEnd, int b0, int bEnd, int dst) : pool(pool), a(a0), aEnd(aEnd), b(b0), bEnd(bEnd), out(dst), aEnded(false), bEnded(false)
     {
         spanA.t0 = spanA.t1 = spanB.t0 = spanB.t1 = 0.0f;
         spanA.tags = spanB.tags = 0u;
@@ -197,9 +198,9 @@ struct MergeCursor
 // Runs one combinator to exhaustion, writing its output spans from `dst` on; returns the slot
 // after the last output.
 template <class P>
-static __device__ __forceinline__ int mergeListsT(const P &pool, int kind, int a0, int b0, int top, int dst)
+static __device__ __forceinline__ int mergeRangesT(const P &pool, int kind, int a0, int aEnd, int b0, int bEnd, int dst)
 {
-    MergeCursor<P> m(pool, a0, b0, top, dst);
+    MergeCursor<P> m(pool, a0, aEnd, b0, bEnd, dst);
     m.nextA();
     m.nextB();
     if(kind == DK_UNION)
@@ -324,6 +325,13 @@ static __device__ __forceinline__ int mergeListsT(const P &pool, int kind, int a
         }
     }
     return m.out;
+}
+
+// The two lists on top of an operand stack: A = [a0, b0), B = [b0, top).
+template <class P>
+static __device__ __forceinline__ int mergeListsT(const P &pool, int kind, int a0, int b0, int top, int dst)
+{
+    return mergeRangesT(pool, kind, a0, b0, b0, top, dst);
 }
 
 static __device__ __noinline__ int mergeLists(const Pool &pool, int kind, int a0, int b0, int top, int dst) { return mergeListsT(pool, kind, a0, b0, top, dst); }

@@ -22,7 +22,7 @@ RENDERS = np.load(os.path.join(common.GOLDEN, "renders.npz"))
 
 # Tolerances (relative to the golden image's mean radiance):
 MEAN_TOL = 0.005      # |mean(gpu) - mean(ref)| / mean(ref)
-RMSE_TOL = {"c1": 0.04, "c2": 0.015, "c4": 0.025, "c5": 0.05}  # per-pixel RMS error / mean(ref); sample counts per case: golden_cases.RENDER_SETUP
+RMSE_TOL = {"c1": 0.03, "c2": 0.01, "c4": 0.012, "c5": 0.05}  # measured on B200: 0.016, 0.0053, 0.0054, 0.025  # per-pixel RMS error / mean(ref); sample counts per case: golden_cases.RENDER_SETUP
 
 
 def test_texture_known_answers():
