@@ -407,7 +407,7 @@ struct FastItem
 // as one leaf and jumps over the subtree's own words.  When a lower end reaches an upper start the
 // reference's result depends on the tree (an extended span is not re-merged with later spans of its own
 // list), so the warp falls through to the subtree's words, which follow the record unchanged.
-static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, int &maxStack, int &poolBound)
+static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, int &maxStack, int &poolBound, FastTree *tree = nullptr)
 {
     auto f2u = [](float f) {
         uint32_t u;
@@ -524,6 +524,13 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
     };
     std::vector<size_t> skipWord(nItems, 0); // SKIP word to patch when item i has been emitted
     std::vector<size_t> leafWord(nItems, (size_t)-1); // header word of every transformed-sphere leaf
+    if(tree)
+    { // what the generator of the register-resident evaluator needs (ptb_specialize.cu): the postfix sequence
+      // itself and where each leaf's (and cluster's) record sits in the stream
+        tree->items.resize(nItems);
+        for(int i = 0; i < nItems; i++)
+            tree->items[i] = FastTreeItem{seq[i].kind, seq[i].prim, seq[i].clusterEnd, -1, -1};
+    }
     size_t header = 0; // word that can still take operators
     bool sealed = true, freshLeaf = false;
     // the open cluster record: it takes the operators that follow its subtree, exactly those the
@@ -592,6 +599,8 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
         { // header {x, tags, extra planes, words to jump}, plane, then {{tags}, plane} per extra plane
             clusterEnd = seq[i].clusterEnd;
             cluster = out.size();
+            if(tree)
+                tree->items[i].clusterWord = (int)cluster;
             out.push_back(make_uint4(FK_PLANE | FH_MISS_SHIFT, tagsOf(seq[i].prim), 0, 0));
             out.push_back(worldPlane(p));
             for(int k = i + 1; k < clusterEnd; k++)
@@ -633,6 +642,8 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
             header = out.size() - 1;
             out.push_back(worldPlane(p));
         }
+        if(tree)
+            tree->items[i].leafWord = (int)header;
         sealed = false;
         freshLeaf = true;
     }
@@ -707,7 +718,7 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
     }
 }
 
-int ptb::sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> *fastOnly, const std::vector<ImageSource> *sources)
+int ptb::sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> *fastOnly, const std::vector<ImageSource> *sources, FastTree *treeOnly)
 {
     if(!d || d->abi_version != PTB200_ABI_VERSION)
         return fail(PTB_EINVAL, "scene description has a different abi_version");
@@ -810,7 +821,8 @@ int ptb::sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> 
     if(sizes.size() != 1)
         return fail(PTB_EINVAL, "CSG program does not leave exactly one object on the stack");
     std::vector<uint4> fast;
-    compileFastProgram(d, fast, maxStack, poolBound);
+    FastTree tree;
+    compileFastProgram(d, fast, maxStack, poolBound, &tree);
     if(maxStack > PTB_FAST_MAX_STACK)
         return fail(PTB_EINVAL, "CSG tree needs more than 32 pending operands (right-deep nesting); rebalance it");
     if(poolBound > 65535)
@@ -818,9 +830,12 @@ int ptb::sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> 
     if(fastOnly)
     { // ptb200_specialize_probe: validation and the compiled stream only, no device
         *fastOnly = fast;
+        if(treeOnly)
+            *treeOnly = tree;
         return PTB_OK;
     }
     s->fastHost = fast;
+    s->fastTree = tree;
     prog.push_back(make_uint4(DK_END, 0, 0, 0));
 
     std::vector<float4> geo(d->n_prims);
@@ -1065,7 +1080,7 @@ static int chooseSpec(PtbScene *s, uint32_t flags, double work, int which, SpecC
         return PTB_OK;
     }
     if(s->specSource[which].empty())
-        s->specSource[which] = specializeSource(s->fastHost, which);
+        s->specSource[which] = specializeSource(s->fastHost, s->fastTree, which);
     const int mode = force || specMode() == 1 ? SPEC_WAIT : work >= 67108864.0 ? SPEC_START : SPEC_PEEK;
     std::string err;
     const SpecKernels *k = specializeGet(s->specSource[which], s->device, mode, err);
@@ -1189,9 +1204,23 @@ extern "C" int ptb200_specialize_probe(const PtbSceneDesc *desc, int which, char
     try
     {
         std::vector<uint4> fast;
-        if(int rc = sceneCreateImpl(desc, nullptr, &fast))
+        FastTree tree;
+        if(int rc = sceneCreateImpl(desc, nullptr, &fast, nullptr, &tree))
             return rc;
-        const std::string src = specializeSource(fast, which);
+        std::string src;
+        if(which == 2)
+        { // the compiled fast stream itself, one word per line (tests: the CPU emulation of the evaluators runs the
+          // interpreter over these words beside the generated code)
+            char buf[64];
+            for(const uint4 &w : fast)
+            {
+                snprintf(buf, sizeof(buf), "%08x %08x %08x %08x\n", w.x, w.y, w.z, w.w);
+                src += buf;
+            }
+            cubin_bytes = nullptr;
+        }
+        else
+            src = specializeSource(fast, tree, which);
         if(source_length)
             *source_length = src.size();
         if(source && source_capacity)

@@ -37,7 +37,9 @@
 namespace ptb
 {
 
+#ifndef PTB_HOST_EMU
 extern __shared__ uint4 ptbSmem[];
+#endif
 
 // header.x: bits 0-3 one-hot kind (cheap bit tests, no jump table), 4-5 leaf action / control
 // sub-kind, 6 = shift the bit stack when the leaf misses (action == PUSH), 7 = the word has a tail
@@ -93,6 +95,12 @@ enum
 #endif
 #define PTB_FAST_MAX_STACK 32
 
+#ifdef PTB_HOST_EMU
+static inline uint4 lds128(uint32_t a) { uint4 v; memcpy(&v, PTB_EMU_SMEM + a, 16); return v; }
+static inline uint32_t lds32(uint32_t a) { uint32_t v; memcpy(&v, PTB_EMU_SMEM + a, 4); return v; }
+static inline void sts32(uint32_t a, uint32_t v) { memcpy(PTB_EMU_SMEM + a, &v, 4); }
+static inline void sts128(uint32_t a, uint4 v) { memcpy(PTB_EMU_SMEM + a, &v, 16); }
+#else
 __device__ __forceinline__ uint4 lds128(uint32_t a)
 {
     uint4 v;
@@ -107,6 +115,8 @@ __device__ __forceinline__ uint32_t lds32(uint32_t a)
 }
 __device__ __forceinline__ void sts32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 __device__ __forceinline__ void sts128(uint32_t a, uint4 v) { asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory"); }
+
+#endif
 
 // Span pool in shared memory with a global overflow area for slots >= cap.
 struct FastPool
@@ -171,6 +181,10 @@ struct FastCtx
     }
 };
 
+#ifdef PTB_HOST_EMU
+static inline float rcpApprox(float x) { return 1.0f / x; }
+static inline float sqrtApprox(float x) { return sqrtf(x); }
+#else
 __device__ __forceinline__ float rcpApprox(float x)
 {
     float r;
@@ -183,6 +197,7 @@ __device__ __forceinline__ float sqrtApprox(float x)
     asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
+#endif
 
 // Evaluator state of one ray.
 struct FastState

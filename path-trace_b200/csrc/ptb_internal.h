@@ -86,6 +86,7 @@ struct PtbScene
     // scene-specialised trace kernels (ptb_specialize.cu): compiled on first use by a render or ray batch
     // large enough to pay for the compile, or at once with PTB_FLAG_SPECIALIZE
     std::vector<uint4> fastHost;
+    ptb::FastTree fastTree;
     std::string specSource[2]; // SPEC_TRACE, SPEC_INTERSECT
     int lastSpecPasses = 0, lastPasses = 0; // of the last render call with stats
     int specSeen[2] = {0, 0};               // calls that wanted the specialised kernels of each kind so far
@@ -129,7 +130,7 @@ struct ImageSource
 {
     const float4 *device; // NULL: take PtbImageDesc::rgba
 };
-int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> *fastOnly = nullptr, const std::vector<ImageSource> *sources = nullptr);
+int sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> *fastOnly = nullptr, const std::vector<ImageSource> *sources = nullptr, FastTree *treeOnly = nullptr);
 int checkParams(const PtbRenderParams *p, int &x0, int &y0, int &rw, int &rh);
 // The wavefront driver.  Caller holds scene->lock and has made scene->device current.
 int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbStats *stats, cudaStream_t stream, const PixelListArg *points = nullptr);

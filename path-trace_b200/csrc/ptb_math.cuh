@@ -9,7 +9,9 @@
 //                       reciprocal / rsqrt; relative error ~1e-7..1e-6, inside the 1e-5 gate of
 //                       BASELINE.json.  This is the policy the renderer runs.
 #pragma once
-#ifndef __CUDACC_RTC__
+#if defined(PTB_HOST_EMU)
+#include "ptb_host_emu.h" /* tests only: the evaluators compiled as host code, one lane at a time */
+#elif !defined(__CUDACC_RTC__)
 #include <cuda_runtime.h>
 #include <stdint.h>
 #endif
@@ -44,9 +46,13 @@ struct Ar
     {
         if(EX)
             return __fsqrt_rn(a);
+#ifdef PTB_HOST_EMU
+        return sqrtf(a);
+#else
         float r;
         asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
         return r;
+#endif
     }
     static __device__ __forceinline__ V3 add(V3 a, V3 b) { return mk(add(a.x, b.x), add(a.y, b.y), add(a.z, b.z)); }
     static __device__ __forceinline__ V3 sub(V3 a, V3 b) { return mk(sub(a.x, b.x), sub(a.y, b.y), sub(a.z, b.z)); }

@@ -15,6 +15,7 @@
 #include <thread>
 #include <vector>
 
+#include "ptb200.h"
 #include "ptb_specialize.h"
 #include "ptb_csg_fast.cuh"
 
@@ -127,7 +128,7 @@ std::string label(size_t w) { return "W" + std::to_string(w); }
 // One labelled block per record of the fast stream (formats: ptb_csg_fast.cuh, compileFastProgram in
 // ptb_capi.cu).  Every block is the body of one trip of evalFast's loop with the record's words as
 // literals; PTB_ADVANCE becomes fall-through or goto.
-std::string specializeSource(const std::vector<uint4> &prog, int which)
+static std::string specializeSourceGen1(const std::vector<uint4> &prog, int which)
 {
     std::string s;
     if(const char *e = getenv("PTB_SPEC_MIN_CTAS")) // experiment: resident CTAs per SM the trace kernels are compiled for; default 8 = 64 registers (C5 camera-ray trace: 6 -> 288 ms, 7 -> 272, 8 -> 267, 10 -> 306 with spills, 12 -> 318)
@@ -223,6 +224,251 @@ std::string specializeSource(const std::vector<uint4> &prog, int which)
                  "    ptb::specSharedInit(cap, overflow, ovfStride);\n    ptb::intersectFastBody<true, " +
                  (o0 ? "true" : "false") + ">(sc, cap, overflow, ovfStride, origins, dirs, n, hits, spans, maxSpans);\n}\n";
     return s;
+}
+
+// ---- second generation: one list variable per node of the tree, lists of up to two spans in registers ---------------
+// (ptb_csg_reg.cuh).  The code is generated from the postfix sequence (the TREE) and takes every leaf's constants
+// from the compiled fast stream, so the leaf arithmetic — and with it every t, tag and list length — is the
+// interpreter's.
+namespace
+{
+struct GenNode
+{
+    int item;        // index into FastTree::items
+    int left, right; // operator: node ids of its operands; leaf: -1
+    int firstItem;   // first sequence item of the subtree
+};
+struct Gen
+{
+    const std::vector<uint4> &prog;
+    const FastTree &tree;
+    std::vector<GenNode> nodes;
+    std::string s;
+    Gen(const std::vector<uint4> &prog, const FastTree &tree) : prog(prog), tree(tree) {}
+
+    static std::string var(int id) { return "L" + std::to_string(id); }
+    void line(int indent, const std::string &text) { s += std::string(4 * (size_t)indent, ' ') + text + "\n"; }
+    bool isCluster(int id) const
+    {
+        const GenNode &n = nodes[id];
+        return n.left >= 0 && tree.items[n.firstItem].clusterEnd == n.item && tree.items[n.firstItem].clusterWord >= 0;
+    }
+    // code of one plane record -> RList (a single plane, or the planes of a cluster folded in registers)
+    void planeFoldCalls(int indent, size_t w, uint32_t extra)
+    {
+        line(indent, "float loEnd = -3.0e38f, upStart = 3.0e38f, lt0, lt1, ut0;");
+        line(indent, "uint32_t loTags = 0u, upTags = 0u, ltags, utags;");
+        line(indent, "bool full = false, hit, two;");
+        line(indent, "planeFold<O0>(" + u4(prog[w + 1]) + ", " + hex(prog[w].y) + ", o, d, loEnd, upStart, loTags, upTags, full);");
+        for(uint32_t j = 0; j < extra; j++)
+            line(indent, "planeFold<O0>(" + u4(prog[w + 3 + 2 * j]) + ", " + hex(prog[w + 2 + 2 * j].x) + ", o, d, loEnd, upStart, loTags, upTags, full);");
+    }
+    void leaf(int id, int indent)
+    {
+        const FastTreeItem &it = tree.items[nodes[id].item];
+        const size_t w = (size_t)it.leafWord;
+        const uint4 h = prog[w];
+        line(indent, "RList " + var(id) + ";");
+        line(indent, "{");
+        if(h.x & FK_PLANE)
+        { // PlaneSpanIterator::init, src/plane.cpp:35-63
+            planeFoldCalls(indent + 1, w, 0u);
+            line(indent + 1, "planeFinish(loEnd, upStart, loTags, upTags, full, hit, two, lt0, lt1, ut0, ltags, utags);");
+            line(indent + 1, var(id) + " = rlCluster(ev, hit, two, lt0, lt1, ut0, ltags, utags);");
+        }
+        else
+        { // SphereSpanIterator::init, src/sphere.cpp:31-49
+            line(indent + 1, "float a, b, e, t0 = 0.f, t1 = 0.f;");
+            if(h.x & FK_SPHERE_XF)
+                line(indent + 1, "xfDisc<O0>(" + u4(h) + ", " + u4(prog[w + 1]) + ", " + u4(prog[w + 2]) + ", " + u4(prog[w + 3]) + ", o, d, a, b, e);");
+            else
+                line(indent + 1, "sphereDisc<O0>(" + u4(h) + ", " + u4(prog[w + 1]) + ", o, d, a, b, e);");
+            line(indent + 1, "if(e > PTB_EPS)");
+            line(indent + 1, "{");
+            line(indent + 2, "const float q = sqrtApprox(e), ia = rcpApprox(a);");
+            line(indent + 2, "t0 = (-b - q) * ia, t1 = (-b + q) * ia;");
+            line(indent + 1, "}");
+            line(indent + 1, var(id) + " = rlLeaf(e > PTB_EPS, t0, t1, " + hex(h.y) + ");");
+        }
+        line(indent, "}");
+    }
+    // The right operand of the root Union, a leaf or a plane cluster, as registers: nB spans b0, b1 (nB = -1: a
+    // cluster whose half-lines cross, to be evaluated leaf by leaf).
+    void rootRight(int id, int indent)
+    {
+        const GenNode &n = nodes[id];
+        line(indent, "int nB = -1;");
+        line(indent, "SpanRec b0 = rlSpan(0.f, 0.f, 0u), b1 = b0;");
+        line(indent, "{");
+        const FastTreeItem &first = tree.items[n.firstItem];
+        const size_t w = (size_t)(n.left < 0 ? first.leafWord : first.clusterWord);
+        const uint4 h = prog[w];
+        if(h.x & FK_PLANE)
+        {
+            const uint32_t extra = n.left < 0 ? 0u : h.z;
+            planeFoldCalls(indent + 1, w, extra);
+            if(extra >= 2u)
+                line(indent + 1, "if(!full && loEnd < upStart)");
+            else if(extra == 1u)
+                line(indent + 1, "if(!full)");
+            line(indent + 1, "{");
+            line(indent + 2, "planeFinish(loEnd, upStart, loTags, upTags, full, hit, two, lt0, lt1, ut0, ltags, utags);");
+            line(indent + 2, "nB = hit ? (two ? 2 : 1) : 0;");
+            line(indent + 2, "b0 = rlSpan(lt0, lt1, ltags), b1 = rlSpan(ut0, PTB_MAX_VALUE, utags);");
+            line(indent + 1, "}");
+        }
+        else
+        {
+            line(indent + 1, "float a, b, e;");
+            if(h.x & FK_SPHERE_XF)
+                line(indent + 1, "xfDisc<O0>(" + u4(h) + ", " + u4(prog[w + 1]) + ", " + u4(prog[w + 2]) + ", " + u4(prog[w + 3]) + ", o, d, a, b, e);");
+            else
+                line(indent + 1, "sphereDisc<O0>(" + u4(h) + ", " + u4(prog[w + 1]) + ", o, d, a, b, e);");
+            line(indent + 1, "nB = 0;");
+            line(indent + 1, "if(e > PTB_EPS)");
+            line(indent + 1, "{");
+            line(indent + 2, "const float q = sqrtApprox(e), ia = rcpApprox(a);");
+            line(indent + 2, "nB = 1, b0 = rlSpan((-b - q) * ia, (-b + q) * ia, " + hex(h.y) + ");");
+            line(indent + 1, "}");
+        }
+        line(indent, "}");
+    }
+    void node(int id, int indent, bool asCluster = true)
+    {
+        const GenNode &n = nodes[id];
+        if(n.left < 0)
+        {
+            leaf(id, indent);
+            return;
+        }
+        if(asCluster && isCluster(id))
+        { // a Union-only subtree of planes: folded in registers while every lower end lies below every upper start
+          // (compileFastProgram has the proof), else its leaves are merged one by one like any other subtree
+            const size_t w = (size_t)tree.items[n.firstItem].clusterWord;
+            const uint32_t extra = prog[w].z;
+            line(indent, "RList " + var(id) + ";");
+            line(indent, "{");
+            planeFoldCalls(indent + 1, w, extra);
+            line(indent + 1, std::string("if(!full && (") + (extra == 1u ? "true" : "loEnd < upStart") + "))");
+            line(indent + 1, "{");
+            line(indent + 2, "planeFinish(loEnd, upStart, loTags, upTags, full, hit, two, lt0, lt1, ut0, ltags, utags);");
+            line(indent + 2, var(id) + " = rlCluster(ev, hit, two, lt0, lt1, ut0, ltags, utags);");
+            line(indent + 1, "}");
+            line(indent + 1, "else");
+            line(indent + 1, "{");
+            node(id, indent + 2, false); // declares L<id>_sub
+            line(indent + 2, var(id) + " = " + var(id) + "_sub;");
+            line(indent + 1, "}");
+            line(indent, "}");
+            return;
+        }
+        const int kind = tree.items[n.item].kind;
+        node(n.left, indent);
+        if(kind == PTB_OP_UNION)
+            node(n.right, indent);
+        else
+        { // {} \ B = {} n B = {}: the right operand of a lane whose left one is empty is never evaluated
+            line(indent, "RList " + var(n.right) + "_r = rlEmpty();");
+            line(indent, "if(" + var(n.left) + ".n != 0)");
+            line(indent, "{");
+            node(n.right, indent + 1);
+            line(indent + 1, var(n.right) + "_r = " + var(n.right) + ";");
+            line(indent, "}");
+        }
+        const std::string rhs = kind == PTB_OP_UNION ? var(n.right) : var(n.right) + "_r";
+        const char *fn = kind == PTB_OP_UNION ? "rlUnion" : kind == PTB_OP_DIFFERENCE ? "rlDifference" : "rlIntersection";
+        line(indent, "RList " + var(id) + (asCluster ? "" : "_sub") + " = " + fn + "(ev, " + var(n.left) + ", " + rhs + ");");
+    }
+};
+} // namespace
+
+static std::string specializeSourceGen2(const std::vector<uint4> &prog, const FastTree &tree, int which)
+{
+    Gen g(prog, tree);
+    std::vector<int> stack;
+    for(size_t i = 0; i < tree.items.size(); i++)
+    {
+        GenNode n;
+        n.item = (int)i, n.left = n.right = -1, n.firstItem = (int)i;
+        if(tree.items[i].kind != PTB_OP_PUSH_PRIM)
+        {
+            n.right = stack.back();
+            stack.pop_back();
+            n.left = stack.back();
+            stack.pop_back();
+            n.firstItem = g.nodes[n.left].firstItem;
+        }
+        g.nodes.push_back(n);
+        stack.push_back((int)g.nodes.size() - 1);
+    }
+    const int root = stack.back();
+    std::string s;
+    if(const char *e = getenv("PTB_SPEC_MIN_CTAS"))
+        s += "#define PTB_TRACE_MIN_CTAS " + std::to_string(atoi(e)) + "\n";
+    s += "#include \"ptb200.h\"\n#include \"ptb_csg_reg.cuh\"\nnamespace ptb\n{\n";
+    const GenNode &rn = g.nodes[root];
+    const bool fusedRoot = which == SPEC_TRACE && rn.left >= 0 && tree.items[rn.item].kind == PTB_OP_UNION && !g.isCluster(root) &&
+                           (g.nodes[rn.right].left < 0 || g.isCluster(rn.right));
+    if(which == SPEC_TRACE)
+    { // the renderer's trace kernels only want the first boundary with t >= eps
+        g.s += "template <bool O0>\n__device__ __forceinline__ int specTrace(REval &ev, const V3 o, const V3 d, float &t, uint32_t &tag)\n{\n";
+        if(fusedRoot)
+        { // the root Union is scanned while it is merged; its right operand (a leaf or a plane cluster) stays in registers
+            g.node(rn.left, 1);
+            g.rootRight(rn.right, 1);
+            g.line(1, "if(nB >= 0)");
+            g.line(2, "return rlUnionFirstHit(ev, " + Gen::var(rn.left) + ", nB, b0, b1, t, tag);");
+            if(g.isCluster(rn.right) && prog[(size_t)tree.items[g.nodes[rn.right].firstItem].clusterWord].z >= 2u)
+            { // a cluster of three or more planes whose half-lines cross: its leaves one by one, then the root as a list
+                g.node(rn.right, 1, false);
+                g.line(1, "const RList Lroot = rlUnion(ev, " + Gen::var(rn.left) + ", " + Gen::var(rn.right) + "_sub);");
+                g.line(1, "return rlFirstHit(ev, Lroot, t, tag);");
+            }
+            else
+                g.line(1, "return PTB_HIT_MISS; // (not reached)");
+        }
+        else
+        {
+            g.node(root, 1);
+            g.line(1, "return rlFirstHit(ev, " + Gen::var(root) + ", t, tag);");
+        }
+        g.s += "}\n";
+    }
+    else
+    { // ray batches want the whole root list: pool slots [0, n)
+        g.s += "template <bool O0>\n__device__ __forceinline__ int specList(REval &ev, const V3 o, const V3 d)\n{\n";
+        g.node(root, 1);
+        g.line(1, "return rlToPool(ev, " + Gen::var(root) + ");");
+        g.s += "}\n";
+    }
+    s += g.s;
+    s += "} // namespace ptb\n";
+    s += "#define PTB_SPEC_GEN 2\n#include \"ptb_trace.cuh\"\n";
+    if(which == SPEC_TRACE)
+    {
+        s += "extern \"C\" __global__ void __launch_bounds__(PTB_FAST_THREADS, PTB_TRACE_MIN_CTAS) ptbSpecTracePrimary(ptb::DevScene sc, int cap, float *overflow, size_t ovfStride, "
+             "ptb::RenderPass pass, uint2 *hits)\n{\n    ptb::tracePrimaryBody<true>(sc, cap, overflow, ovfStride, pass, hits);\n}\n";
+        s += "extern \"C\" __global__ void __launch_bounds__(PTB_FAST_THREADS, PTB_TRACE_MIN_CTAS) ptbSpecTraceQueue(ptb::DevScene sc, int cap, float *overflow, size_t ovfStride, "
+             "ptb::RayQueue in, const unsigned *inCount, uint2 *hits)\n{\n    ptb::traceQueueBody<true>(sc, cap, overflow, ovfStride, in, inCount, hits);\n}\n";
+    }
+    else
+        for(int o0 = 0; o0 < 2; o0++)
+            s += std::string("extern \"C\" __global__ void __launch_bounds__(PTB_FAST_THREADS) ptbSpecIntersect") + (o0 ? "O0" : "") +
+                 "(ptb::DevScene sc, int cap, float *overflow, size_t ovfStride, const float4 *origins, const float4 *dirs, size_t n, PtbHit *hits, PtbSpan *spans, int maxSpans)\n{\n"
+                 "    ptb::intersectFastBody<true, " +
+                 (o0 ? "true" : "false") + ">(sc, cap, overflow, ovfStride, origins, dirs, n, hits, spans, maxSpans);\n}\n";
+    return s;
+}
+
+std::string specializeSource(const std::vector<uint4> &prog, const FastTree &tree, int which)
+{
+    static const int gen = [] {
+        const char *e = getenv("PTB_SPEC_GEN");
+        return e ? atoi(e) : 2;
+    }();
+    if(gen == 1 || tree.items.empty())
+        return specializeSourceGen1(prog, which);
+    return specializeSourceGen2(prog, tree, which);
 }
 
 int specializeCompile(const std::string &source, std::vector<char> &cubin, std::string &log)

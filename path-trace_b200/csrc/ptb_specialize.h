@@ -27,7 +27,23 @@ enum
     SPEC_TRACE = 0,
     SPEC_INTERSECT = 1
 };
-std::string specializeSource(const std::vector<uint4> &fastProgram, int which);
+// The postfix CSG sequence the fast stream was compiled from, with the stream position of every leaf record: what
+// the generator of the register-resident evaluator walks (it needs the TREE; the stream only has its flattening).
+struct FastTreeItem
+{
+    int kind;        // PTB_OP_*
+    int prim;        // PUSH_PRIM: the primitive
+    int clusterEnd;  // first leaf of a plane cluster: sequence index of the Union that completes it, else -1
+    int leafWord;    // PUSH_PRIM: word index of the leaf's own header in the fast stream
+    int clusterWord; // first leaf of a plane cluster: word index of the cluster record
+};
+struct FastTree
+{
+    std::vector<FastTreeItem> items;
+};
+// PTB_SPEC_GEN=1 selects the first-generation generator (one labelled block per stream record, pool + bit stack);
+// the default is the register-resident evaluator (ptb_csg_reg.cuh).
+std::string specializeSource(const std::vector<uint4> &fastProgram, const FastTree &tree, int which);
 // NVRTC: source -> sm_100a cubin.  Needs no GPU.  0 on success; log has the compiler's output.
 int specializeCompile(const std::string &source, std::vector<char> &cubin, std::string &log);
 // The kernels compiled from `source` (specializeSource), loaded into the current context of `device`.

@@ -20,11 +20,59 @@
 #define PTB_TRACE_TRIP_SYNC()
 #endif
 #ifndef PTB_EVAL
+#if defined(PTB_SPEC_GEN) && PTB_SPEC_GEN == 2
+#define PTB_EVAL(GP, O0, R, cx, gprog, o, d, tops) tops[0] = specEvalList<O0>(cx, gprog, o[0], d[0])
+#else
 #define PTB_EVAL(GP, O0, R, cx, gprog, o, d, tops) evalFast<GP, O0, R>(cx, gprog, o, d, tops)
+#endif
 #endif
 
 namespace ptb
 {
+
+#if defined(PTB_SPEC_GEN) && PTB_SPEC_GEN == 2
+// Register-resident evaluator of ONE scene (generated: specTrace / specList, ptb_csg_reg.cuh).  A ray whose lists
+// outgrow the shared pool flags it; the warp (all 32 lanes are here: idle ones carry null rays) is then rerun
+// through the interpreter, which has the global overflow area — same spans, more instructions.
+template <bool O0>
+__device__ __forceinline__ REval specBegin(const FastCtx &cx)
+{
+    REval ev;
+    ev.poolBase = cx.pool.base, ev.cap = cx.pool.cap, ev.top = 0, ev.ovf = false;
+    return ev;
+}
+template <bool O0>
+__device__ __forceinline__ int specEvalList(const FastCtx &cx, const uint4 *__restrict__ gprog, V3 o, V3 d)
+{
+    REval ev = specBegin<O0>(cx);
+    int n = specList<O0>(ev, o, d);
+    if(__any_sync(0xFFFFFFFFu, ev.ovf))
+    {
+        V3 oo[1] = {o}, dd[1] = {d};
+        int tops[1];
+        evalFast<true, O0, 1>(cx, gprog, oo, dd, tops);
+        n = tops[0];
+    }
+    return n;
+}
+template <bool O0>
+__device__ __forceinline__ uint2 specTraceHit(const DevScene &sc, const FastCtx &cx, V3 o, V3 d)
+{
+    REval ev = specBegin<O0>(cx);
+    float t = -1.f;
+    uint32_t tag = 0u;
+    int kind = specTrace<O0>(ev, o, d, t, tag);
+    if(__any_sync(0xFFFFFFFFu, ev.ovf))
+    {
+        V3 oo[1] = {o}, dd[1] = {d};
+        int tops[1];
+        evalFast<true, O0, 1>(cx, sc.fastProgram, oo, dd, tops);
+        t = -1.f, tag = 0u;
+        kind = firstHit(cx.pool, tops[0], t, tag);
+    }
+    return make_uint2(__float_as_uint(t), ((uint32_t)kind << 16) | tag);
+}
+#endif
 
 // Fast evaluator: stage the program (unless GP: it stays in global memory) and lay out the pools
 // and start stacks of the R rays each thread carries.
@@ -201,6 +249,9 @@ __device__ __forceinline__ void cameraSample(const RenderPass &pass, unsigned nP
 template <bool GP, bool O0>
 __device__ __forceinline__ void traceRays(const DevScene &sc, const FastCtx &cx, const V3 (&o)[PTB_TRACE_RAYS], const V3 (&d)[PTB_TRACE_RAYS], uint2 (&h)[PTB_TRACE_RAYS])
 {
+#if defined(PTB_SPEC_GEN) && PTB_SPEC_GEN == 2
+    h[0] = specTraceHit<O0>(sc, cx, o[0], d[0]); // (the generated modules carry one ray per lane)
+#else
     int tops[PTB_TRACE_RAYS];
     PTB_EVAL(GP, O0, PTB_TRACE_RAYS, cx, sc.fastProgram, o, d, tops);
 #pragma unroll
@@ -211,6 +262,7 @@ __device__ __forceinline__ void traceRays(const DevScene &sc, const FastCtx &cx,
         int kind = firstHit(cx.poolOf(r), tops[r], t, tag);
         h[r] = make_uint2(__float_as_uint(t), ((uint32_t)kind << 16) | tag);
     }
+#endif
 }
 
 // A warp takes 32 * PTB_TRACE_RAYS consecutive rays per trip: lane l carries rays l, l + 32, ...
