@@ -1094,7 +1094,10 @@ static int chooseSpec(PtbScene *s, uint32_t flags, double work, int which, SpecC
     const DevScene &dev = s->dev;
     CsgConfig &cfg = sp.cfg;
     cfg.threads = PTB_FAST_THREADS, cfg.fast = 1, cfg.stageProgram = 0;
-    cfg.cap = std::min(dev.poolBound, 12);
+    // (the register-resident evaluator appends every general merge above its operands and has no overflow area of
+    // its own — a ray that outgrows the pool reruns through the interpreter — so it gets 16 slots: 24 KB per CTA)
+    static const bool gen1 = getenv("PTB_SPEC_GEN") && atoi(getenv("PTB_SPEC_GEN")) == 1;
+    cfg.cap = std::min(dev.poolBound, gen1 ? 12 : 16);
     if(const char *e = getenv("PTB200_POOL_CAP")) // tests: force lists into the global overflow area
         cfg.cap = std::max(2, std::min(dev.poolBound, atoi(e)));
     cfg.smemBytes = fastSharedBytes(dev, cfg.cap, false, 1);

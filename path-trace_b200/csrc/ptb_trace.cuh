@@ -41,18 +41,27 @@ __device__ __forceinline__ REval specBegin(const FastCtx &cx)
     ev.poolBase = cx.pool.base, ev.cap = cx.pool.cap, ev.top = 0, ev.ovf = false;
     return ev;
 }
+// The interpreter as the rare way out, out of line and with plain arguments so that it does not weigh on the
+// register allocation of the generated code.  Returns the length of the root list (pool slots [0, n)).
+template <bool O0>
+static __device__ __noinline__ int specFallback(const uint4 *__restrict__ gprog, uint32_t poolBase, int cap, float *ovf, size_t ovfStride, uint32_t stk, float ox, float oy, float oz,
+                                                float dx, float dy, float dz)
+{
+    FastCtx cx;
+    cx.prog = 0u, cx.stk = stk, cx.stkStride = 0u, cx.poolStride = 0u, cx.ovfRay = 0;
+    cx.pool.base = poolBase, cx.pool.cap = cap, cx.pool.ovf = ovf, cx.pool.ovfStride = ovfStride;
+    V3 oo[1] = {mk(ox, oy, oz)}, dd[1] = {mk(dx, dy, dz)};
+    int tops[1];
+    evalFast<true, O0, 1>(cx, gprog, oo, dd, tops);
+    return tops[0];
+}
 template <bool O0>
 __device__ __forceinline__ int specEvalList(const FastCtx &cx, const uint4 *__restrict__ gprog, V3 o, V3 d)
 {
     REval ev = specBegin<O0>(cx);
     int n = specList<O0>(ev, o, d);
     if(__any_sync(0xFFFFFFFFu, ev.ovf))
-    {
-        V3 oo[1] = {o}, dd[1] = {d};
-        int tops[1];
-        evalFast<true, O0, 1>(cx, gprog, oo, dd, tops);
-        n = tops[0];
-    }
+        n = specFallback<O0>(gprog, cx.pool.base, cx.pool.cap, cx.pool.ovf, cx.pool.ovfStride, cx.stk, o.x, o.y, o.z, d.x, d.y, d.z);
     return n;
 }
 template <bool O0>
@@ -64,11 +73,9 @@ __device__ __forceinline__ uint2 specTraceHit(const DevScene &sc, const FastCtx 
     int kind = specTrace<O0>(ev, o, d, t, tag);
     if(__any_sync(0xFFFFFFFFu, ev.ovf))
     {
-        V3 oo[1] = {o}, dd[1] = {d};
-        int tops[1];
-        evalFast<true, O0, 1>(cx, sc.fastProgram, oo, dd, tops);
+        const int n = specFallback<O0>(sc.fastProgram, cx.pool.base, cx.pool.cap, cx.pool.ovf, cx.pool.ovfStride, cx.stk, o.x, o.y, o.z, d.x, d.y, d.z);
         t = -1.f, tag = 0u;
-        kind = firstHit(cx.pool, tops[0], t, tag);
+        kind = firstHit(cx.pool, n, t, tag);
     }
     return make_uint2(__float_as_uint(t), ((uint32_t)kind << 16) | tag);
 }

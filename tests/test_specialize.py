@@ -1,6 +1,8 @@
-"""Scene-specialised trace kernels (path-trace_b200/csrc/ptb_specialize.cu): the compiled CSG stream of a
-scene printed as straight-line CUDA and compiled with NVRTC at run time.  They must compute exactly what
-the interpreting kernels compute: same device functions, program words as literals.
+"""Scene-specialised trace kernels (path-trace_b200/csrc/ptb_specialize.cu): the CSG tree of a scene printed
+as CUDA — one span-list variable per node, single spans in registers (csrc/ptb_csg_reg.cuh), every leaf's
+constants literals — and compiled with NVRTC at run time.  They must compute exactly what the interpreting
+kernels compute: same leaf arithmetic, same merge state machines.  (tests/test_spec_emulation.py checks the same
+on the CPU.)
 
 CPU: the generated source compiles for sm_100a (NVRTC needs no GPU).  GPU: bitwise identity with the
 interpreter on ray batches (hits and whole span lists) and on rendered frames (ray counts; pixels up to
@@ -22,10 +24,10 @@ def test_generated_source_compiles_for_sm100a():
     for world, which in ((scenes.config5(b), 0), (scenes.config3(b), 1), (scenes.random_tree(b, 7, 9), 0)):
         flat = device.Flat(world)
         source, cubin = device.specialize_probe(flat, which)
-        assert "evalSpec" in source and "W0:" in source and "goto WEND;" in source
+        assert ("specTrace" if which == 0 else "specList") in source and "rlUnion(ev, " in source and "ptb_csg_reg.cuh" in source
         assert ("ptbSpecTracePrimary" in source) == (which == 0) and ("ptbSpecIntersectO0" in source) == (which == 1)
         assert cubin > 10000
-    # every record of the stream has its block: one label per leaf and control word
+    # every leaf of the tree has its code
     flat = device.Flat(scenes.config4(b))
     source, _ = device.specialize_probe(flat, 0, compile=False)
     assert source.count("xfDisc<O0>") >= 48 and source.count("planeFold<O0>") >= 22
