@@ -234,7 +234,7 @@ def kernel_rooflines(name, desc, st, n_pix, passes, fp32_peak_tflops, hbm_peak_g
         ("trace_primary", spec, "fp32", st.ms_trace_primary, st.rays_primary, st.rays_primary * (fpr + CAMERA_FLOPS), "%d flop/ray (model %d + camera %d)" % (fpr + CAMERA_FLOPS, fpr, CAMERA_FLOPS)),
         ("shade_primary", "shadeKernel<primary>", "hbm", st.ms_shade_primary, st.rays_primary,
          8.0 * st.rays_primary + 64.0 * st.rays_first_bounce + 32.0 * n_pix * passes, "8 B/path + 64 B/survivor + 32 B/pixel/pass"),
-        ("trace_bounce", "traceQueueKernel (interpreter)", "fp32", st.ms_trace_bounce, st.rays_bounce, st.rays_bounce * fpr, "%d flop/ray" % fpr),
+        ("trace_bounce", "ptbSpecTraceQueue (scene-specialised, NVRTC)" if spec_all and os.environ.get("PTB_SPEC_BOUNCE", "1") != "0" else "traceQueueKernel (interpreter)", "fp32", st.ms_trace_bounce, st.rays_bounce, st.rays_bounce * fpr, "%d flop/ray" % fpr),
         ("shade_bounce", "shadeKernel<bounce>", "hbm", st.ms_shade_bounce, st.rays_bounce,
          72.0 * st.rays_bounce + 64.0 * survivors_bounce + 32.0 * finished_bounce, "72 B/ray + 64 B/survivor + 32 B/finished path"),
     ]

@@ -1507,12 +1507,13 @@ int ptb::renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbS
     pass.flags = p->flags;
     uint64_t launches = 0;
     int specPasses = 0;
-    // Queued (bounce) rays are incoherent: nearly every leaf is hit by some lane of the warp, the
-    // specialised block then calls its out-of-line half and ends up behind the interpreter's single inline
-    // site (C5: 211-231 ms against 207-222).  They stay interpreted unless the caller forces
-    // specialisation (the parity tests do) or PTB_SPEC_BOUNCE=1.
-    static const bool specBounceEnv = getenv("PTB_SPEC_BOUNCE") && atoi(getenv("PTB_SPEC_BOUNCE")) != 0;
-    const bool specBounce = specBounceEnv || (p->flags & PTB_FLAG_SPECIALIZE) != 0;
+    // Queued (bounce) rays run the specialised kernels too.  (The first generation — pool, bit stack, one out-of-line
+    // push-and-operate call per leaf some lane hit — lost on these incoherent rays, C5 211-231 ms against the
+    // interpreter's 207-222, and kept them interpreted; the register-resident evaluator has no such call and no
+    // warp votes: C5 bounce trace 196 -> 104 ms per frame, profiles/r02c_*.)  PTB_SPEC_BOUNCE=0 keeps them interpreted.
+    static const int specBounceEnv = getenv("PTB_SPEC_BOUNCE") ? atoi(getenv("PTB_SPEC_BOUNCE")) : -1;
+    static const bool specGen1 = getenv("PTB_SPEC_GEN") && atoi(getenv("PTB_SPEC_GEN")) == 1;
+    const bool specBounce = specBounceEnv >= 0 ? specBounceEnv != 0 : (!specGen1 || (p->flags & PTB_FLAG_SPECIALIZE) != 0);
     for(int i = 0; i < nPasses; i++)
     {
         unsigned *c = (unsigned *)sx.counters.p + (size_t)i * (stages + 1);
