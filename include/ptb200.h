@@ -248,6 +248,23 @@ int ptb200_intersect(PtbScene *scene, const float *origins, const float *dirs, s
 int ptb200_intersect_device(PtbScene *scene, const void *d_origins4, const void *d_dirs4, size_t n,
                             void *d_hits, void *d_spans, int max_spans, uint32_t flags, void *stream);
 
+/* ptb200_intersect_device WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, same kernels (the interpreting ones: PTB_FLAG_SPECIALIZE is refused, a
+ * run-time compile allocates) and the same results as ptb200_intersect_device; the kernels' scratch — the span-pool
+ * overflow area that span lists longer than the shared-memory pool spill to — is a static device array of
+ * PTB_STATIC_SCRATCH_BYTES (16 MiB, held by every GPU that loads the library until exit) instead of a cudaMalloc'ed
+ * block, and the grid shrinks (never below one CTA per SM) until it fits.  PTB_EINVAL with a message that names both
+ * sizes when the scene's worst-case span lists need more than that at one CTA per SM (about 73 spans beyond the shared
+ * pool per ray on a 148-SM B200).  Calls no cudaMalloc / cudaFree / allocating library routine; asynchronous on
+ * <stream>.  Every call on a GPU shares the one array: calls that overlap on that GPU race on it — serialise them
+ * (one stream, or events).  Nothing in the array needs clearing between calls: the kernels write a slot before they
+ * read it.  _static_scratch_bytes returns PTB_STATIC_SCRATCH_BYTES. */
+#define PTB_STATIC_SCRATCH_BYTES (16u << 20)
+int ptb200_intersect_device_static(PtbScene *scene, const void *d_origins4, const void *d_dirs4, size_t n, void *d_hits, void *d_spans, int max_spans, uint32_t flags,
+                                   void *stream);
+size_t ptb200_static_scratch_bytes(void);
+
 /* Evaluates texture program <tex_root> at n positions (n x 3 floats, host): the reference's
  * Texture::getColor -> rgb (n x 3) and Texture::getFloat -> f (n); either output may be NULL. */
 int ptb200_texture_eval(PtbScene *scene, int tex_root, const float *positions, size_t n,

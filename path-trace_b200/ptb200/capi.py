@@ -100,7 +100,7 @@ ABI_SYMBOLS = [
     "ptb200_intersect", "ptb200_intersect_device", "ptb200_texture_eval", "ptb200_render", "ptb200_render_adaptive", "ptb200_render_accumulate_device", "ptb200_resolve_device", "ptb200_display8_device", "ptb200_display8",
     "ptb200_render_async", "ptb200_job_done", "ptb200_job_read", "ptb200_job_wait", "ptb200_job_destroy", "ptb200_sample_scatter", "ptb200_fp32_peak", "ptb200_specialize_probe", "ptb200_scene_specialized", "ptb200_tile_request_parse", "ptb200_tile_encode", "ptb200_tile_decode",
     "ptb200_comm_unique_id", "ptb200_comm_init_rank", "ptb200_comm_init_all", "ptb200_comm_info", "ptb200_comm_destroy", "ptb200_scene_create_multi", "ptb200_render_multi",
-    "ptb200_multi_rows", "ptb200_multi_shard", "ptb200_vector_eval", "ptb200_rng_words", "ptb200_render_pixels",
+    "ptb200_multi_rows", "ptb200_multi_shard", "ptb200_vector_eval", "ptb200_rng_words", "ptb200_render_pixels", "ptb200_intersect_device_static", "ptb200_static_scratch_bytes",
 ]
 
 _vp, _f, _i, _sz = C.c_void_p, C.c_float, C.c_int, C.c_size_t
@@ -211,6 +211,8 @@ def product():
         lib.ptb200_tile_decode.argtypes = [C.c_char_p, _sz, _i, _i, _i, _vp, _vp, C.POINTER(_i), C.POINTER(_sz)]
         lib.ptb200_fp32_peak.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double)]
         _ip = C.POINTER(_i)
+        lib.ptb200_intersect_device_static.argtypes = [_vp, _vp, _vp, _sz, _vp, _vp, _i, C.c_uint32, _vp]
+        lib.ptb200_static_scratch_bytes.restype = _sz
         lib.ptb200_render_pixels.argtypes = [_vp, C.POINTER(PtbRenderParams), _vp, _sz, _vp, C.POINTER(PtbStats)]
         lib.ptb200_vector_eval.argtypes = [_i, _vp, _vp, _vp, _sz, _vp]
         lib.ptb200_rng_words.argtypes = [_i, C.c_uint64, _vp, _vp, _vp, _sz, _vp]
