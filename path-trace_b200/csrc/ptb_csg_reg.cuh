@@ -300,6 +300,43 @@ __device__ __forceinline__ RList rlIntersection(REval &ev, const RList &A, const
     return rlGeneral(ev, DK_INTERSECTION, A, B);
 }
 
+// The same three, accumulating into the left operand (what the generated code calls: a node's list variable is
+// its left operand's, so A u {} = A costs nothing at all).
+__device__ __forceinline__ void rlUnionInto(REval &ev, RList &A, const RList &B)
+{
+    if(B.n == 0)
+        return;
+    if(A.n == 0)
+        A = B;
+    else if(A.n == 1 && B.n == 1)
+        A = rlUnion11(ev, A.a, B.a);
+    else
+        A = rlGeneral(ev, DK_UNION, A, B);
+}
+__device__ __forceinline__ void rlDifferenceInto(REval &ev, RList &A, const RList &B)
+{
+    if(B.n == 0 || A.n == 0)
+        return; // (the right operand of an empty left one is never evaluated: nothing to release)
+    if(A.n == 1 && B.n == 1)
+        A = rlDifference11(ev, A.a, B.a);
+    else
+        A = rlGeneral(ev, DK_DIFFERENCE, A, B);
+}
+__device__ __forceinline__ void rlIntersectionInto(REval &ev, RList &A, const RList &B)
+{
+    if(A.n == 0)
+        return;
+    if(B.n == 0)
+    {
+        rlRelease(ev, A, B);
+        A.n = 0;
+    }
+    else if(A.n == 1 && B.n == 1)
+        A = rlIntersection11(A.a, B.a);
+    else
+        A = rlGeneral(ev, DK_INTERSECTION, A, B);
+}
+
 // ---- the root -----------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ SpanRec rlGet(const REval &ev, const RList &L, int i)
 {
@@ -385,7 +422,9 @@ __device__ __forceinline__ int rlUnionFirstHit(const REval &ev, const RList &A, 
             }
             continue;
         }
-        const int k = rlScanSpan(fromB ? sb : sa, t, tag);
+        SpanRec cur; // (field by field: a `fromB ? sb : sa` reference becomes an address select through local memory)
+        cur.t0 = fromB ? sb.t0 : sa.t0, cur.t1 = fromB ? sb.t1 : sa.t1, cur.tags = fromB ? sb.tags : sa.tags;
+        const int k = rlScanSpan(cur, t, tag);
         if(k >= 0)
             return k;
         if(fromB)

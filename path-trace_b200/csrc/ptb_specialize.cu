@@ -246,7 +246,13 @@ struct Gen
     std::string s;
     Gen(const std::vector<uint4> &prog, const FastTree &tree) : prog(prog), tree(tree) {}
 
-    static std::string var(int id) { return "L" + std::to_string(id); }
+    std::vector<int> alias; // node -> node whose list variable holds its result (an operator accumulates into its left operand)
+    std::string var(int id) const
+    {
+        while(id < (int)alias.size() && alias[id] != id)
+            id = alias[id];
+        return "L" + std::to_string(id);
+    }
     void line(int indent, const std::string &text) { s += std::string(4 * (size_t)indent, ' ') + text + "\n"; }
     bool isCluster(int id) const
     {
@@ -357,7 +363,7 @@ struct Gen
             line(indent + 1, "else");
             line(indent + 1, "{");
             node(id, indent + 2, false); // declares L<id>_sub
-            line(indent + 2, var(id) + " = " + var(id) + "_sub;");
+            line(indent + 2, "L" + std::to_string(id) + " = L" + std::to_string(id) + "_sub;");
             line(indent + 1, "}");
             line(indent, "}");
             return;
@@ -368,16 +374,21 @@ struct Gen
             node(n.right, indent);
         else
         { // {} \ B = {} n B = {}: the right operand of a lane whose left one is empty is never evaluated
-            line(indent, "RList " + var(n.right) + "_r = rlEmpty();");
+            const std::string rname = "L" + std::to_string(n.right) + "_r"; // (explicit: var() of the operand changes once it aliases its own left child)
+            line(indent, "RList " + rname + " = rlEmpty();");
             line(indent, "if(" + var(n.left) + ".n != 0)");
             line(indent, "{");
             node(n.right, indent + 1);
-            line(indent + 1, var(n.right) + "_r = " + var(n.right) + ";");
+            line(indent + 1, rname + " = " + var(n.right) + ";");
             line(indent, "}");
         }
-        const std::string rhs = kind == PTB_OP_UNION ? var(n.right) : var(n.right) + "_r";
-        const char *fn = kind == PTB_OP_UNION ? "rlUnion" : kind == PTB_OP_DIFFERENCE ? "rlDifference" : "rlIntersection";
-        line(indent, "RList " + var(id) + (asCluster ? "" : "_sub") + " = " + fn + "(ev, " + var(n.left) + ", " + rhs + ");");
+        const std::string rhs = kind == PTB_OP_UNION ? var(n.right) : "L" + std::to_string(n.right) + "_r";
+        const char *fn = kind == PTB_OP_UNION ? "rlUnionInto" : kind == PTB_OP_DIFFERENCE ? "rlDifferenceInto" : "rlIntersectionInto";
+        line(indent, std::string(fn) + "(ev, " + var(n.left) + ", " + rhs + ");");
+        if(asCluster)
+            alias[id] = n.left; // from here on this node's list IS the left operand's variable
+        else
+            line(indent, "RList L" + std::to_string(id) + "_sub = " + var(n.left) + ";");
     }
 };
 } // namespace
@@ -402,6 +413,9 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
         stack.push_back((int)g.nodes.size() - 1);
     }
     const int root = stack.back();
+    g.alias.resize(g.nodes.size());
+    for(size_t i = 0; i < g.alias.size(); i++)
+        g.alias[i] = (int)i;
     std::string s;
     if(const char *e = getenv("PTB_SPEC_MIN_CTAS"))
         s += "#define PTB_TRACE_MIN_CTAS " + std::to_string(atoi(e)) + "\n";
@@ -417,11 +431,11 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
             g.node(rn.left, 1);
             g.rootRight(rn.right, 1);
             g.line(1, "if(nB >= 0)");
-            g.line(2, "return rlUnionFirstHit(ev, " + Gen::var(rn.left) + ", nB, b0, b1, t, tag);");
+            g.line(2, "return rlUnionFirstHit(ev, " + g.var(rn.left) + ", nB, b0, b1, t, tag);");
             if(g.isCluster(rn.right) && prog[(size_t)tree.items[g.nodes[rn.right].firstItem].clusterWord].z >= 2u)
             { // a cluster of three or more planes whose half-lines cross: its leaves one by one, then the root as a list
                 g.node(rn.right, 1, false);
-                g.line(1, "const RList Lroot = rlUnion(ev, " + Gen::var(rn.left) + ", " + Gen::var(rn.right) + "_sub);");
+                g.line(1, "const RList Lroot = rlUnion(ev, " + g.var(rn.left) + ", " + "L" + std::to_string(rn.right) + "_sub);");
                 g.line(1, "return rlFirstHit(ev, Lroot, t, tag);");
             }
             else
@@ -430,7 +444,7 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
         else
         {
             g.node(root, 1);
-            g.line(1, "return rlFirstHit(ev, " + Gen::var(root) + ", t, tag);");
+            g.line(1, "return rlFirstHit(ev, " + g.var(root) + ", t, tag);");
         }
         g.s += "}\n";
     }
@@ -438,7 +452,7 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
     { // ray batches want the whole root list: pool slots [0, n)
         g.s += "template <bool O0>\n__device__ __forceinline__ int specList(REval &ev, const V3 o, const V3 d)\n{\n";
         g.node(root, 1);
-        g.line(1, "return rlToPool(ev, " + Gen::var(root) + ");");
+        g.line(1, "return rlToPool(ev, " + g.var(root) + ");");
         g.s += "}\n";
     }
     s += g.s;
