@@ -882,6 +882,13 @@ int ptb::sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> 
             else
                 mats[i].trcF = v.w;
         }
+        // A vertex on such a material ends its path after the emission term whatever the geometry: no refraction
+        // (transmit_reflect_coefficient is the constant 0, path-trace.h:110-111) and a zero reflectance, whose child
+        // contributes exactly 0 (:161).  Every sky material is like that (src/test.cpp:99-105); the shade kernels then
+        // skip the surface normal (ptb_shade.cuh).
+        const int both = (1 << PTB_MAT_TRC) | (1 << PTB_MAT_REFLECT);
+        if((mats[i].constMask & both) == both && !(mats[i].trcF > 0.f) && mats[i].reflect.x == 0.f && mats[i].reflect.y == 0.f && mats[i].reflect.z == 0.f)
+            mats[i].constMask |= PTB_MAT_TERMINAL;
     }
     std::vector<int2> texops(d->n_texops);
     for(int i = 0; i < d->n_texops; i++)
@@ -1518,6 +1525,7 @@ int ptb::renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbS
     {
         unsigned *c = (unsigned *)sx.counters.p + (size_t)i * (stages + 1);
         pass.samplesThisPass = std::min(perPass, p->spp - i * perPass);
+        pass.bySamples = FastDivisor::make((uint32_t)pass.samplesThisPass);
         pass.sampleBase = (int)((long long)p->sample_offset + (long long)i * perPass * p->sample_stride);
         cudaEvent_t *ev = timed ? &sx.events[(size_t)i * evPerPass] : nullptr;
         if(timed)

@@ -180,6 +180,28 @@ __device__ __forceinline__ void accumulate(float4 *accum, uint32_t pixel, V3 rad
         atomicAdd(&accum[pixel], make_float4(rad.x, rad.y, rad.z, done));
 }
 
+// The same for a whole warp (all 32 lanes must call it): lanes are summed over runs of equal `pixel` first — with the
+// pixel-major work order a warp holds one or two pixels — and the first lane of each run issues the atomic.  Lanes
+// with nothing to add pass pixel = 0xFFFFFFFF.
+__device__ __forceinline__ void accumulateWarp(float4 *accum, uint32_t pixel, V3 rad, float done, unsigned lane)
+{
+    const uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, pixel, 1);
+    const bool head = lane == 0u || prev != pixel;
+    const unsigned heads = __ballot_sync(0xFFFFFFFFu, head);
+    const unsigned after = lane == 31u ? 0xFFFFFFFFu : (heads >> (lane + 1u)) | (0xFFFFFFFFu << (31u - lane)); // bit k-1: lane + k starts a new run (or is past the warp)
+    float x = rad.x, y = rad.y, z = rad.z, w = done;
+#pragma unroll
+    for(unsigned d = 1u; d < 32u; d <<= 1)
+    {
+        const float tx = __shfl_down_sync(0xFFFFFFFFu, x, d), ty = __shfl_down_sync(0xFFFFFFFFu, y, d), tz = __shfl_down_sync(0xFFFFFFFFu, z, d),
+                    tw = __shfl_down_sync(0xFFFFFFFFu, w, d);
+        if((after & ((1u << d) - 1u)) == 0u) // lanes lane+1 .. lane+d all belong to this lane's run
+            x += tx, y += ty, z += tz, w += tw;
+    }
+    if(head && pixel != 0xFFFFFFFFu && (x != 0.f || y != 0.f || z != 0.f || w != 0.f))
+        atomicAdd(&accum[pixel], make_float4(x, y, z, w));
+}
+
 // One path vertex from a packed hit record (t, kind << 16 | boundary tag): normal through the un-folded
 // transform chain, material, relative ior (path-trace.h:72-95), then shadeVertex.  Adds the vertex's radiance to
 // `rad`; true while the path goes on (ps then holds the next ray).
@@ -191,12 +213,16 @@ __device__ __forceinline__ bool shadeHitRecord(const DevScene &sc, const RenderP
     const uint32_t tag = h.y & 0xFFFFu;
     Hit hit;
     hit.t = __uint_as_float(h.x);
-    V3 n = boundaryNormal<false>(sc, tag, hit.t, ps.o, ps.d);
     hit.mat = __ldg(&sc.primMeta[tag >> 1]).y;
-    if(kind == PTB_HIT_ENTER)
-        hit.n = n, hit.ior = sc.materials[hit.mat].iorIn; // path-trace.h:72-81
-    else
-        hit.n = neg(n), hit.ior = sc.materials[hit.mat].ior; // path-trace.h:86-95
+    hit.n = mk(0.f, 0.f, 0.f), hit.ior = 1.f;
+    if(!(sc.materials[hit.mat].constMask & PTB_MAT_TERMINAL))
+    { // (a terminal material — every sky plane — never looks at the normal: two thirds of the camera hits of C5)
+        V3 n = boundaryNormal<false>(sc, tag, hit.t, ps.o, ps.d);
+        if(kind == PTB_HIT_ENTER)
+            hit.n = n, hit.ior = sc.materials[hit.mat].iorIn; // path-trace.h:72-81
+        else
+            hit.n = neg(n), hit.ior = sc.materials[hit.mat].ior; // path-trace.h:86-95
+    }
     Philox rng;
     rngInit(rng, pass.seed, ps.pixel, ps.sample, ps.rngBlock);
     const bool alive = shadeVertex(sc, ps, hit, rng, pass.flags, rad);
@@ -236,6 +262,8 @@ __global__ void __launch_bounds__(PTB_SHADE_THREADS, PRIMARY ? PTB_SHADE_MIN_CTA
         unsigned long long i = base + lane;
         bool alive = false;
         PathState ps;
+        V3 rad = mk(0.f, 0.f, 0.f);
+        uint32_t accPixel = 0xFFFFFFFFu;
         const uint2 h = hNext;
         const float4 c0 = n0, c1 = n1, c2 = n2, c3 = n3;
         if(i + stride < total)
@@ -255,10 +283,10 @@ __global__ void __launch_bounds__(PTB_SHADE_THREADS, PRIMARY ? PTB_SHADE_MIN_CTA
                 ps.thr = mk(c2.x, c2.y, c2.z), ps.sample = __float_as_uint(c2.w);
                 ps.depth = __float_as_uint(c3.x), ps.rngBlock = __float_as_uint(c3.y);
             }
-            V3 rad = mk(0.f, 0.f, 0.f);
             alive = shadeHitRecord(sc, pass, ps, h, rad);
-            accumulate(accum, ps.pixel, rad, alive ? 0.f : 1.f);
+            accPixel = ps.pixel;
         }
+        accumulateWarp(accum, accPixel, rad, (accPixel != 0xFFFFFFFFu && !alive) ? 1.f : 0.f, lane);
         // survivors go to the warp's staging buffer in shared memory; full groups of 32 are flushed
         // with ONE atomic on the queue counter and four fully coalesced 512-byte stores.  (ncu: with
         // one atomic per warp iteration 20 % of the kernel's stall samples sat on its return value.)

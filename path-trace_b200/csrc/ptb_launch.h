@@ -74,6 +74,7 @@ struct RenderPass
     float sw, sh, sd;
     float twoOverWidth, twoOverHeight; // 2 / width, 2 / height
     FastDivisor byPixels, byRowWidth;  // rw * rh and rw
+    FastDivisor bySamples;             // samplesThisPass
     uint64_t seed;
     uint32_t flags;
     // adaptive rendering: when non-null, sample index p of a pass names lattice point pixelList[p]

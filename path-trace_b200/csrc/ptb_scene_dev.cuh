@@ -13,12 +13,13 @@ struct DevImage
     int w, h;
 };
 
+#define PTB_MAT_TERMINAL (1 << 8) /* constMask: a path ends on this material after the emission term (no refraction, zero reflectance) */
 struct DevMaterial
 {
     int tex[5];  // PTB_MAT_* texture roots
     float ior;   // relative ior when leaving the material (include/path-trace.h:93)
     float iorIn; // float(1.0 / ior): relative ior when entering (include/path-trace.h:79)
-    int constMask; // bit k: texture k is a bare ColorTexture whose value is folded into the fields below
+    int constMask; // bit k: texture k is a bare ColorTexture whose value is folded into the fields below; PTB_MAT_TERMINAL
     // folded constants (rgb, getFloat = mean rgb): one 16-byte load instead of texops -> texdata chains
     float4 emissive, reflect, transmit;
     float scatterF, trcF, pad0, pad1;
