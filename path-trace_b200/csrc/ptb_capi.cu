@@ -1078,7 +1078,12 @@ static int chooseSpec(PtbScene *s, uint32_t flags, double work, int which, SpecC
     // specialised unless the caller insists.
     static const size_t maxWords = [] {
         const char *e = getenv("PTB_SPEC_MAX_WORDS");
-        return e && atoi(e) > 0 ? (size_t)atoi(e) : (size_t)96;
+        if(e && atoi(e) > 0)
+            return (size_t)atoi(e);
+        // (the register-resident generator shares one function among subtrees of the same shape, so the 70 leaves
+        // of config 4 compile to a dozen leaves of code: its limit is compile time, not the instruction cache)
+        const char *g = getenv("PTB_SPEC_GEN");
+        return g && atoi(g) == 1 ? (size_t)96 : (size_t)512;
     }();
     if((flags & (PTB_FLAG_INTERPRET | PTB_FLAG_EXACT)) || (!force && (specMode() == 0 || s->fastHost.size() > maxWords)) || s->fastHost.size() > 4096)
     {

@@ -14,6 +14,7 @@
 #define __device__
 #define __host__
 #define __global__
+#define __constant__ static const
 #define __forceinline__ inline
 #define __noinline__
 #define __restrict__

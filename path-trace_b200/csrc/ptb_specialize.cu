@@ -9,6 +9,8 @@
 #include <string.h>
 
 #include <chrono>
+#include <algorithm>
+#include <functional>
 #include <map>
 #include <mutex>
 #include <string>
@@ -259,15 +261,169 @@ struct Gen
         const GenNode &n = nodes[id];
         return n.left >= 0 && tree.items[n.firstItem].clusterEnd == n.item && tree.items[n.firstItem].clusterWord >= 0;
     }
+    // ---- where a leaf's constants come from: literals, or (inside a shape function) words of the instance's table ----
+    bool tableMode = false;
+    std::map<size_t, int> tabOff; // word of the prototype's records -> offset in an instance's table
+    std::string W(size_t w) const { return tableMode ? "ptbTab[tb + " + std::to_string(tabOff.at(w)) + "]" : u4(prog[w]); }
+    std::string Wy(size_t w) const { return tableMode ? W(w) + ".y" : hex(prog[w].y); }
+    std::string Wx(size_t w) const { return tableMode ? W(w) + ".x" : hex(prog[w].x); }
+
+    // ---- shape functions --------------------------------------------------------------------------------------------
+    // Subtrees of the same SHAPE (same operators, same kinds of leaves, different constants: the eight groups of
+    // six transformed spheres cut by two planes of BASELINE config 4) share one out-of-line function that reads its
+    // leaves' constants from a table in constant memory.  The code of a 70-leaf scene then is a dozen leaves long
+    // and stays in the instruction cache (the first generation's 54 KB of straight-line code per kernel did not:
+    // `no_instruction` 15-36 stall cycles per issue, profiles/r01m_spec_c4.txt).
+    std::vector<std::string> sig; // per node
+    std::vector<int> leaves;      // per node
+    std::map<std::string, int> shapeFn;    // chosen signature -> function number
+    std::map<std::string, int> shapeProto; // chosen signature -> the node whose code becomes the function's body
+    std::vector<std::string> fnDefs;
+    std::vector<bool> fnDone;
+    std::vector<uint4> table; // all instances' constants
+    bool inFn = false;
+
+    size_t leafWords(size_t w) const { return (prog[w].x & FK_SPHERE_XF) ? 4u : (prog[w].x & FK_PLANE) ? 2u : 2u; }
+    void collectWords(int id, std::vector<size_t> &out) const
+    { // the records a subtree's code reads, in the order of its code
+        const GenNode &n = nodes[id];
+        if(n.left < 0)
+        {
+            const size_t w = (size_t)tree.items[n.item].leafWord;
+            for(size_t k = 0; k < leafWords(w); k++)
+                out.push_back(w + k);
+            return;
+        }
+        if(isCluster(id))
+        {
+            const size_t w = (size_t)tree.items[n.firstItem].clusterWord;
+            for(size_t k = 0; k < 2u + 2u * prog[w].z; k++)
+                out.push_back(w + k);
+        }
+        collectWords(n.left, out);
+        collectWords(n.right, out);
+    }
+    void computeShapes()
+    {
+        sig.resize(nodes.size()), leaves.resize(nodes.size());
+        for(size_t id = 0; id < nodes.size(); id++)
+        { // (children precede their parents in `nodes`)
+            const GenNode &n = nodes[id];
+            if(n.left < 0)
+            {
+                const uint32_t x = prog[(size_t)tree.items[n.item].leafWord].x;
+                sig[id] = (x & FK_SPHERE_XF) ? "S" : (x & FK_PLANE) ? "P" : "s";
+                leaves[id] = 1;
+                continue;
+            }
+            const int kind = tree.items[n.item].kind;
+            sig[id] = std::string(isCluster((int)id) ? "C" : "") + (kind == PTB_OP_UNION ? "U(" : kind == PTB_OP_DIFFERENCE ? "D(" : "I(") + sig[n.left] + "," + sig[n.right] + ")";
+            leaves[id] = leaves[n.left] + leaves[n.right];
+        }
+    }
+    // Chooses the shapes: most instances first, larger first among equals; a shape is skipped when one of its
+    // instances contains, or lies inside, an instance of a shape already chosen.
+    void chooseShapes(int root, int minLeaves)
+    {
+        std::map<std::string, std::vector<int>> byShape;
+        for(size_t id = 0; id < nodes.size(); id++)
+            if(leaves[id] >= minLeaves && (int)id != root)
+                byShape[sig[id]].push_back((int)id);
+        std::vector<std::pair<std::pair<int, int>, std::string>> order;
+        for(auto &kv : byShape)
+            if(kv.second.size() >= 2)
+                order.push_back({{-(int)kv.second.size(), -leaves[kv.second[0]]}, kv.first});
+        std::sort(order.begin(), order.end());
+        std::vector<int> covered(nodes.size(), 0); // 1: inside a chosen instance, 2: contains one
+        std::vector<int> parent(nodes.size(), -1);
+        for(size_t id = 0; id < nodes.size(); id++)
+            if(nodes[id].left >= 0)
+                parent[nodes[id].left] = parent[nodes[id].right] = (int)id;
+        std::function<void(int)> markInside = [&](int id) {
+            covered[id] |= 1;
+            if(nodes[id].left >= 0)
+                markInside(nodes[id].left), markInside(nodes[id].right);
+        };
+        for(auto &o : order)
+        {
+            const std::vector<int> &inst = byShape[o.second];
+            bool ok = true;
+            for(int id : inst)
+                ok = ok && covered[id] == 0;
+            if(!ok)
+                continue;
+            shapeFn[o.second] = (int)shapeFn.size();
+            shapeProto[o.second] = inst[0];
+            for(int id : inst)
+            {
+                markInside(id);
+                for(int up = parent[id]; up >= 0; up = parent[up])
+                    covered[up] |= 2;
+            }
+        }
+        fnDone.assign(shapeFn.size(), false);
+        fnDefs.assign(shapeFn.size(), std::string());
+    }
+    int ensureFn(const std::string &sg)
+    {
+        const int f = shapeFn.at(sg), proto = shapeProto.at(sg);
+        if(fnDone[f])
+            return f;
+        fnDone[f] = true;
+        std::string keep;
+        keep.swap(s);
+        std::vector<size_t> words;
+        collectWords(proto, words);
+        tabOff.clear();
+        for(size_t k = 0; k < words.size(); k++)
+            tabOff[words[k]] = (int)k;
+        tableMode = inFn = true;
+        s += "// shape " + sg + "\n";
+        s += "template <bool O0>\nstatic __device__ __noinline__ uint4 ptbShape" + std::to_string(f) +
+             "(uint32_t poolBase, int cap, int top, float ox, float oy, float oz, float dx, float dy, float dz, int tb)\n{\n";
+        line(1, "REval ev;");
+        line(1, "ev.poolBase = poolBase, ev.cap = cap, ev.top = top, ev.ovf = false;");
+        line(1, "const V3 o = mk(ox, oy, oz), d = mk(dx, dy, dz);");
+        node(proto, 1, true, true);
+        const std::string r = var(proto);
+        line(1, "return make_uint4((uint32_t)" + r + ".n | (ev.ovf ? 0x80000000u : 0u), __float_as_uint(" + r + ".a.t0), __float_as_uint(" + r + ".a.t1), " + r + ".a.tags);");
+        s += "}\n";
+        alias[proto] = proto;
+        tableMode = inFn = false;
+        fnDefs[f] = s;
+        s.swap(keep);
+        return f;
+    }
+    // A subtree of a chosen shape: its constants go to the table, its code is a call.  The callee starts with an
+    // empty stack of its own on top of ours, so a result of two or more spans lies at our `top` (ptb_csg_reg.cuh).
+    void emitCall(int id, int indent)
+    {
+        const int f = ensureFn(sig[id]);
+        std::vector<size_t> words;
+        collectWords(id, words);
+        const size_t base = table.size();
+        for(size_t w : words)
+            table.push_back(prog[w]);
+        const std::string L = "L" + std::to_string(id);
+        line(indent, "RList " + L + ";");
+        line(indent, "{");
+        line(indent + 1, "const uint4 r_ = ptbShape" + std::to_string(f) + "<O0>(ev.poolBase, ev.cap, ev.top, o.x, o.y, o.z, d.x, d.y, d.z, " + std::to_string(base) + ");");
+        line(indent + 1, L + ".n = (int)(r_.x & 0x7FFFFFFFu), " + L + ".a = rlSpan(__uint_as_float(r_.y), __uint_as_float(r_.z), r_.w), " + L + ".base = ev.top;");
+        line(indent + 1, "ev.ovf = ev.ovf || (r_.x >> 31) != 0u;");
+        line(indent + 1, "if(" + L + ".n >= 2)");
+        line(indent + 2, "ev.top += " + L + ".n;");
+        line(indent, "}");
+    }
+
     // code of one plane record -> RList (a single plane, or the planes of a cluster folded in registers)
     void planeFoldCalls(int indent, size_t w, uint32_t extra)
     {
         line(indent, "float loEnd = -3.0e38f, upStart = 3.0e38f, lt0, lt1, ut0;");
         line(indent, "uint32_t loTags = 0u, upTags = 0u, ltags, utags;");
         line(indent, "bool full = false, hit, two;");
-        line(indent, "planeFold<O0>(" + u4(prog[w + 1]) + ", " + hex(prog[w].y) + ", o, d, loEnd, upStart, loTags, upTags, full);");
+        line(indent, "planeFold<O0>(" + W(w + 1) + ", " + Wy(w) + ", o, d, loEnd, upStart, loTags, upTags, full);");
         for(uint32_t j = 0; j < extra; j++)
-            line(indent, "planeFold<O0>(" + u4(prog[w + 3 + 2 * j]) + ", " + hex(prog[w + 2 + 2 * j].x) + ", o, d, loEnd, upStart, loTags, upTags, full);");
+            line(indent, "planeFold<O0>(" + W(w + 3 + 2 * j) + ", " + Wx(w + 2 + 2 * j) + ", o, d, loEnd, upStart, loTags, upTags, full);");
     }
     void leaf(int id, int indent)
     {
@@ -286,15 +442,15 @@ struct Gen
         { // SphereSpanIterator::init, src/sphere.cpp:31-49
             line(indent + 1, "float a, b, e, t0 = 0.f, t1 = 0.f;");
             if(h.x & FK_SPHERE_XF)
-                line(indent + 1, "xfDisc<O0>(" + u4(h) + ", " + u4(prog[w + 1]) + ", " + u4(prog[w + 2]) + ", " + u4(prog[w + 3]) + ", o, d, a, b, e);");
+                line(indent + 1, "xfDisc<O0>(" + W(w) + ", " + W(w + 1) + ", " + W(w + 2) + ", " + W(w + 3) + ", o, d, a, b, e);");
             else
-                line(indent + 1, "sphereDisc<O0>(" + u4(h) + ", " + u4(prog[w + 1]) + ", o, d, a, b, e);");
+                line(indent + 1, "sphereDisc<O0>(" + W(w) + ", " + W(w + 1) + ", o, d, a, b, e);");
             line(indent + 1, "if(e > PTB_EPS)");
             line(indent + 1, "{");
             line(indent + 2, "const float q = sqrtApprox(e), ia = rcpApprox(a);");
             line(indent + 2, "t0 = (-b - q) * ia, t1 = (-b + q) * ia;");
             line(indent + 1, "}");
-            line(indent + 1, var(id) + " = rlLeaf(e > PTB_EPS, t0, t1, " + hex(h.y) + ");");
+            line(indent + 1, var(id) + " = rlLeaf(e > PTB_EPS, t0, t1, " + Wy(w) + ");");
         }
         line(indent, "}");
     }
@@ -339,12 +495,17 @@ struct Gen
         }
         line(indent, "}");
     }
-    void node(int id, int indent, bool asCluster = true)
+    void node(int id, int indent, bool asCluster = true, bool inlineThis = false)
     {
         const GenNode &n = nodes[id];
         if(n.left < 0)
         {
             leaf(id, indent);
+            return;
+        }
+        if(!inlineThis && !inFn && !sig.empty() && shapeFn.count(sig[id]))
+        {
+            emitCall(id, indent);
             return;
         }
         if(asCluster && isCluster(id))
@@ -362,7 +523,7 @@ struct Gen
             line(indent + 1, "}");
             line(indent + 1, "else");
             line(indent + 1, "{");
-            node(id, indent + 2, false); // declares L<id>_sub
+            node(id, indent + 2, false, true); // declares L<id>_sub
             line(indent + 2, "L" + std::to_string(id) + " = L" + std::to_string(id) + "_sub;");
             line(indent + 1, "}");
             line(indent, "}");
@@ -416,6 +577,18 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
     g.alias.resize(g.nodes.size());
     for(size_t i = 0; i < g.alias.size(); i++)
         g.alias[i] = (int)i;
+    { // shape functions for large scenes with repeated subtrees (PTB_SPEC_SHAPES=0 never, =1 whatever the size)
+        const char *e = getenv("PTB_SPEC_SHAPES");
+        const int mode = e ? atoi(e) : -1;
+        int nLeaves = 0;
+        for(const FastTreeItem &it : tree.items)
+            nLeaves += it.kind == PTB_OP_PUSH_PRIM;
+        if(mode != 0 && (mode == 1 || nLeaves >= 24))
+        {
+            g.computeShapes();
+            g.chooseShapes(root, mode == 1 ? 3 : 4);
+        }
+    }
     std::string s;
     if(const char *e = getenv("PTB_SPEC_MIN_CTAS"))
         s += "#define PTB_TRACE_MIN_CTAS " + std::to_string(atoi(e)) + "\n";
@@ -455,6 +628,15 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
         g.line(1, "return rlToPool(ev, " + g.var(root) + ");");
         g.s += "}\n";
     }
+    if(!g.table.empty())
+    {
+        s += "__constant__ uint4 ptbTab[" + std::to_string(g.table.size()) + "] = {\n";
+        for(const uint4 &w : g.table)
+            s += "    {" + hex(w.x) + ", " + hex(w.y) + ", " + hex(w.z) + ", " + hex(w.w) + "},\n";
+        s += "};\n";
+    }
+    for(const std::string &f : g.fnDefs)
+        s += f;
     s += g.s;
     s += "} // namespace ptb\n";
     s += "#define PTB_SPEC_GEN 2\n#include \"ptb_trace.cuh\"\n";

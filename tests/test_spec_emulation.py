@@ -32,7 +32,8 @@ def emulate(tmp_path, name, flat, rays_o, rays_d, origin0, cap=12):
     d = tmp_path / name
     d.mkdir(exist_ok=True)
     (d / "trace.inc").write_text(functions_only(probe_text(flat, 0)))
-    (d / "list.inc").write_text(functions_only(probe_text(flat, 1)))
+    # (both modules carry their own copy of the constant table and the shape functions: one program here, so rename)
+    (d / "list.inc").write_text(functions_only(probe_text(flat, 1)).replace("ptbTab", "ptbTabList").replace("ptbShape", "ptbShapeList"))
     (d / "prog.hex").write_text(probe_text(flat, 2))
     rays = np.concatenate([np.asarray(rays_o, np.float32).reshape(-1, 3), np.asarray(rays_d, np.float32).reshape(-1, 3)], 1)
     rays.tofile(d / "rays.bin")
@@ -62,13 +63,15 @@ def bounce_rays(n, seed, centre=(0, 0, -5.0), spread=2.5):
     return o, d
 
 
-@pytest.mark.parametrize("name", ["c2", "c3", "c5", "c1"])
+@pytest.mark.parametrize("name", ["c2", "c3", "c5", "c1", "c4"])
 def test_generated_evaluator_equals_the_interpreter_on_the_configs(tmp_path, name):
     b = product_builder()
     env = scenes.env_latlong(64, 32)
     img = [scenes.pattern_image(16, 12, 11), scenes.pattern_image(20, 24, 12)]
-    world = {"c2": lambda: scenes.config2(b), "c3": lambda: scenes.config3(b), "c5": lambda: scenes.config5(b, env=env, images=img), "c1": lambda: scenes.config1(b, env=env)}[name]()
+    world = {"c2": lambda: scenes.config2(b), "c3": lambda: scenes.config3(b), "c5": lambda: scenes.config5(b, env=env, images=img), "c1": lambda: scenes.config1(b, env=env), "c4": lambda: scenes.config4(b, images=img)}[name]()
     flat = device.Flat(world)
+    if name == "c4":  # 70 leaves: its eight groups share ONE shape function reading a constant table
+        assert "ptbShape0<O0>" in probe_text(flat, 0) and "__constant__ uint4 ptbTab[" in probe_text(flat, 0)
     o, d = camera_rays(20000, 1)
     st = emulate(tmp_path, name + "_cam", flat, o, d, True, cap=16)  # 16 slots: what the kernels are launched with
     # (config 1 splits its sky planes over three clusters, so its lists are long: a few rays outgrow the shared pool
@@ -76,11 +79,13 @@ def test_generated_evaluator_equals_the_interpreter_on_the_configs(tmp_path, nam
     assert st["rays"] == 20000 and st["overflowed"] <= (40 if name == "c1" else 0)
     if name == "c3":
         o, d = scenes.config3_rays(30000)
+    elif name == "c4":
+        o, d = bounce_rays(30000, 2, centre=(0, 0, -9.0), spread=4.0)
     else:
         o, d = bounce_rays(30000, 2, centre=(0, 0, -5.0))
     st = emulate(tmp_path, name + "_gen", flat, o, d, False, cap=16)
     assert st["hits"] > 1000 and st["overflowed"] < 0.01 * st["rays"]
-    if name in ("c3", "c1"):
+    if name in ("c3", "c1", "c4"):
         assert st["multi_span"] > 100  # the general merges ran
 
 
