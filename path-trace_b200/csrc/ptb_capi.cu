@@ -1053,6 +1053,9 @@ static int chooseConfig(PtbScene *s, int which, DeviceBuffer &overflow, CsgConfi
 // PTB_SPECIALIZE=0 never (unless PTB_FLAG_SPECIALIZE), =1 compile at first use and wait, default: a call
 // with at least 2^26 rays to trace starts the compile in the background and keeps interpreting until
 // the kernels are there (they give the same results, so a frame may switch between passes).
+#ifndef PTB_SPEC_GEN2_MAX_WORDS
+#define PTB_SPEC_GEN2_MAX_WORDS 96 /* measured on B200 (profiles/README.md): config 4's 292 words stay interpreted */
+#endif
 struct SpecConfig
 {
     const SpecKernels *k = nullptr;
@@ -1083,7 +1086,7 @@ static int chooseSpec(PtbScene *s, uint32_t flags, double work, int which, SpecC
         // (the register-resident generator shares one function among subtrees of the same shape, so the 70 leaves
         // of config 4 compile to a dozen leaves of code: its limit is compile time, not the instruction cache)
         const char *g = getenv("PTB_SPEC_GEN");
-        return g && atoi(g) == 1 ? (size_t)96 : (size_t)512;
+        return g && atoi(g) == 1 ? (size_t)96 : (size_t)PTB_SPEC_GEN2_MAX_WORDS;
     }();
     if((flags & (PTB_FLAG_INTERPRET | PTB_FLAG_EXACT)) || (!force && (specMode() == 0 || s->fastHost.size() > maxWords)) || s->fastHost.size() > 4096)
     {
@@ -1113,6 +1116,8 @@ static int chooseSpec(PtbScene *s, uint32_t flags, double work, int which, SpecC
     if(const char *e = getenv("PTB200_POOL_CAP")) // tests: force lists into the global overflow area
         cfg.cap = std::max(2, std::min(dev.poolBound, atoi(e)));
     cfg.smemBytes = fastSharedBytes(dev, cfg.cap, false, 1);
+    if(!gen1)
+        cfg.smemBytes += (size_t)dev.fastWords * 16; // room for the module's constant table behind pools and stacks (never more words than the program has)
     if(cfg.smemBytes > s->smemOptin)
         return PTB_OK;
     const int perSm = specOccupancy(which == SPEC_TRACE ? k->tracePrimary : k->intersect, cfg.threads, cfg.smemBytes);

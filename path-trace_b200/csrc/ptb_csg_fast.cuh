@@ -171,6 +171,7 @@ struct FastCtx
     uint32_t stkStride;  // bytes from ray r's start stack to ray r+1's
     uint32_t poolStride; // bytes from ray r's pool to ray r+1's
     size_t ovfRay;       // floats from ray r's overflow area to ray r+1's
+    uint32_t tab;        // shared address of the constant table of a scene-specialised module (ptb_csg_reg.cuh), behind pools and stacks
     FastPool pool;       // ray 0's pool
     __device__ __forceinline__ FastPool poolOf(int r) const
     {

@@ -45,7 +45,24 @@ struct REval
     int cap;           // slots in shared memory
     int top;           // slots in use
     bool ovf;          // a list did not fit: the result of this ray is void, rerun it through the interpreter
+    uint32_t tab;      // shared address of the module's constant table (shape functions read their leaves' constants there)
 };
+
+// One word of the constant table.  Not volatile: the table is read-only once staged, so the compiler may merge and
+// move these loads.  (In constant memory the same reads were 13 indexed scalar LDCs per transformed sphere and the
+// kernel stalled on the memory-input/output queue: profiles/r02f_full_c4_shapes.txt.)
+#ifdef PTB_HOST_EMU
+static inline uint4 ldsTab128(uint32_t a) { return lds128(a); }
+#else
+__device__ __forceinline__ uint4 ldsTab128(uint32_t a)
+{
+    uint4 v;
+    asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+#endif
+// Defined by the generated module: copies its table (if it has one) to shared memory at `tab`; all threads call it.
+__device__ __forceinline__ void specStageTable(uint32_t tab);
 
 __device__ __forceinline__ void rpoolStore(uint32_t poolBase, int slot, const SpanRec &r)
 {

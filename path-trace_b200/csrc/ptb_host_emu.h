@@ -35,7 +35,8 @@ typedef unsigned long long cudaTextureObject_t;
 typedef void *cudaStream_t;
 
 struct PtbEmuDim { unsigned x, y, z; };
-static const PtbEmuDim threadIdx = {0, 0, 0}, blockIdx = {0, 0, 0}, blockDim = {128, 1, 1}, gridDim = {1, 1, 1};
+static PtbEmuDim threadIdx = {0, 0, 0}; // (a harness may step it to emulate a CTA-wide copy loop)
+static const PtbEmuDim blockIdx = {0, 0, 0}, blockDim = {128, 1, 1}, gridDim = {1, 1, 1};
 
 // shared memory of the one emulated CTA: "shared addresses" are byte offsets into it
 static uint4 ptbEmuShared[16384];

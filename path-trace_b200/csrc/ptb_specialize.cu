@@ -264,9 +264,7 @@ struct Gen
     // ---- where a leaf's constants come from: literals, or (inside a shape function) words of the instance's table ----
     bool tableMode = false;
     std::map<size_t, int> tabOff; // word of the prototype's records -> offset in an instance's table
-    std::string W(size_t w) const { return tableMode ? "ptbTab[tb + " + std::to_string(tabOff.at(w)) + "]" : u4(prog[w]); }
-    std::string Wy(size_t w) const { return tableMode ? W(w) + ".y" : hex(prog[w].y); }
-    std::string Wx(size_t w) const { return tableMode ? W(w) + ".x" : hex(prog[w].x); }
+    std::string W(size_t w) const { return tableMode ? "ldsTab128(tb + " + std::to_string(16 * tabOff.at(w)) + "u)" : u4(prog[w]); }
 
     // ---- shape functions --------------------------------------------------------------------------------------------
     // Subtrees of the same SHAPE (same operators, same kinds of leaves, different constants: the eight groups of
@@ -380,9 +378,9 @@ struct Gen
         tableMode = inFn = true;
         s += "// shape " + sg + "\n";
         s += "template <bool O0>\nstatic __device__ __noinline__ uint4 ptbShape" + std::to_string(f) +
-             "(uint32_t poolBase, int cap, int top, float ox, float oy, float oz, float dx, float dy, float dz, int tb)\n{\n";
+             "(uint32_t poolBase, int cap, int top, float ox, float oy, float oz, float dx, float dy, float dz, uint32_t tb)\n{\n";
         line(1, "REval ev;");
-        line(1, "ev.poolBase = poolBase, ev.cap = cap, ev.top = top, ev.ovf = false;");
+        line(1, "ev.poolBase = poolBase, ev.cap = cap, ev.top = top, ev.ovf = false, ev.tab = 0u;");
         line(1, "const V3 o = mk(ox, oy, oz), d = mk(dx, dy, dz);");
         node(proto, 1, true, true);
         const std::string r = var(proto);
@@ -407,7 +405,7 @@ struct Gen
         const std::string L = "L" + std::to_string(id);
         line(indent, "RList " + L + ";");
         line(indent, "{");
-        line(indent + 1, "const uint4 r_ = ptbShape" + std::to_string(f) + "<O0>(ev.poolBase, ev.cap, ev.top, o.x, o.y, o.z, d.x, d.y, d.z, " + std::to_string(base) + ");");
+        line(indent + 1, "const uint4 r_ = ptbShape" + std::to_string(f) + "<O0>(ev.poolBase, ev.cap, ev.top, o.x, o.y, o.z, d.x, d.y, d.z, ev.tab + " + std::to_string(16 * base) + "u);");
         line(indent + 1, L + ".n = (int)(r_.x & 0x7FFFFFFFu), " + L + ".a = rlSpan(__uint_as_float(r_.y), __uint_as_float(r_.z), r_.w), " + L + ".base = ev.top;");
         line(indent + 1, "ev.ovf = ev.ovf || (r_.x >> 31) != 0u;");
         line(indent + 1, "if(" + L + ".n >= 2)");
@@ -421,9 +419,9 @@ struct Gen
         line(indent, "float loEnd = -3.0e38f, upStart = 3.0e38f, lt0, lt1, ut0;");
         line(indent, "uint32_t loTags = 0u, upTags = 0u, ltags, utags;");
         line(indent, "bool full = false, hit, two;");
-        line(indent, "planeFold<O0>(" + W(w + 1) + ", " + Wy(w) + ", o, d, loEnd, upStart, loTags, upTags, full);");
+        line(indent, "planeFold<O0>(" + W(w + 1) + ", " + W(w) + ".y, o, d, loEnd, upStart, loTags, upTags, full);");
         for(uint32_t j = 0; j < extra; j++)
-            line(indent, "planeFold<O0>(" + W(w + 3 + 2 * j) + ", " + Wx(w + 2 + 2 * j) + ", o, d, loEnd, upStart, loTags, upTags, full);");
+            line(indent, "planeFold<O0>(" + W(w + 3 + 2 * j) + ", " + W(w + 2 + 2 * j) + ".x, o, d, loEnd, upStart, loTags, upTags, full);");
     }
     void leaf(int id, int indent)
     {
@@ -441,16 +439,17 @@ struct Gen
         else
         { // SphereSpanIterator::init, src/sphere.cpp:31-49
             line(indent + 1, "float a, b, e, t0 = 0.f, t1 = 0.f;");
+            line(indent + 1, "const uint4 k0 = " + W(w) + ";");
             if(h.x & FK_SPHERE_XF)
-                line(indent + 1, "xfDisc<O0>(" + W(w) + ", " + W(w + 1) + ", " + W(w + 2) + ", " + W(w + 3) + ", o, d, a, b, e);");
+                line(indent + 1, "xfDisc<O0>(k0, " + W(w + 1) + ", " + W(w + 2) + ", " + W(w + 3) + ", o, d, a, b, e);");
             else
-                line(indent + 1, "sphereDisc<O0>(" + W(w) + ", " + W(w + 1) + ", o, d, a, b, e);");
+                line(indent + 1, "sphereDisc<O0>(k0, " + W(w + 1) + ", o, d, a, b, e);");
             line(indent + 1, "if(e > PTB_EPS)");
             line(indent + 1, "{");
             line(indent + 2, "const float q = sqrtApprox(e), ia = rcpApprox(a);");
             line(indent + 2, "t0 = (-b - q) * ia, t1 = (-b + q) * ia;");
             line(indent + 1, "}");
-            line(indent + 1, var(id) + " = rlLeaf(e > PTB_EPS, t0, t1, " + Wy(w) + ");");
+            line(indent + 1, var(id) + " = rlLeaf(e > PTB_EPS, t0, t1, k0.y);");
         }
         line(indent, "}");
     }
@@ -634,7 +633,11 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
         for(const uint4 &w : g.table)
             s += "    {" + hex(w.x) + ", " + hex(w.y) + ", " + hex(w.z) + ", " + hex(w.w) + "},\n";
         s += "};\n";
+        s += "__device__ __forceinline__ void specStageTable(uint32_t tab)\n{\n    for(uint32_t i = threadIdx.x; i < " + std::to_string(g.table.size()) +
+             "u; i += PTB_FAST_THREADS)\n        sts128(tab + 16u * i, ptbTab[i]);\n}\n";
     }
+    else
+        s += "__device__ __forceinline__ void specStageTable(uint32_t) {}\n";
     for(const std::string &f : g.fnDefs)
         s += f;
     s += g.s;

@@ -38,7 +38,7 @@ template <bool O0>
 __device__ __forceinline__ REval specBegin(const FastCtx &cx)
 {
     REval ev;
-    ev.poolBase = cx.pool.base, ev.cap = cx.pool.cap, ev.top = 0, ev.ovf = false;
+    ev.poolBase = cx.pool.base, ev.cap = cx.pool.cap, ev.top = 0, ev.ovf = false, ev.tab = cx.tab;
     return ev;
 }
 // The interpreter as the rare way out, out of line and with plain arguments so that it does not weigh on the
@@ -48,7 +48,7 @@ static __device__ __noinline__ int specFallback(const uint4 *__restrict__ gprog,
                                                 float dx, float dy, float dz)
 {
     FastCtx cx;
-    cx.prog = 0u, cx.stk = stk, cx.stkStride = 0u, cx.poolStride = 0u, cx.ovfRay = 0;
+    cx.prog = 0u, cx.stk = stk, cx.stkStride = 0u, cx.poolStride = 0u, cx.ovfRay = 0, cx.tab = 0u;
     cx.pool.base = poolBase, cx.pool.cap = cap, cx.pool.ovf = ovf, cx.pool.ovfStride = ovfStride;
     V3 oo[1] = {mk(ox, oy, oz)}, dd[1] = {mk(dx, dy, dz)};
     int tops[1];
@@ -104,6 +104,10 @@ __device__ __forceinline__ FastCtx setupFast(const DevScene &sc, int cap, float 
     c.pool.ovfStride = ovfStride;
     c.ovfRay = (size_t)(sc.poolBound > cap ? sc.poolBound - cap : 0) * 3 * ovfStride;
     c.stk = c.pool.base + (uint32_t)R * c.poolStride;
+    c.tab = base + 16u * words + (uint32_t)R * (c.poolStride + c.stkStride);
+#if defined(PTB_SPEC_GEN) && PTB_SPEC_GEN == 2
+    specStageTable(c.tab); // the generated module's leaf constants: constant memory -> shared memory, once per CTA
+#endif
     __syncthreads();
     return c;
 }

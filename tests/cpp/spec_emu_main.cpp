@@ -15,8 +15,15 @@
 #include "ptb200.h"
 #include "ptb_csg_reg.cuh"
 
+namespace ptb
+{
+inline void specStageTableList(uint32_t tab); // (the list module's copy of specStageTable, renamed by the test)
+}
 #include SPEC_LIST_INC
 #include SPEC_TRACE_INC
+
+// where the two modules' constant tables are staged in the emulated shared memory (pools and stacks lie below)
+static const uint32_t kTabTrace = 96u << 10, kTabList = 160u << 10;
 
 using namespace ptb;
 
@@ -49,7 +56,7 @@ static int run(const std::vector<uint4> &prog, const std::vector<float> &rays, i
         hits += wkind != 0, multi += tops[0] >= 2;
         // generated code, list flavour
         REval ev;
-        ev.poolBase = 0, ev.cap = cap, ev.top = 0, ev.ovf = false;
+        ev.poolBase = 0, ev.cap = cap, ev.top = 0, ev.ovf = false, ev.tab = kTabList;
         const int got = specList<O0>(ev, o, d);
         bool ovf = ev.ovf, ok = true;
         if(!ovf)
@@ -64,7 +71,7 @@ static int run(const std::vector<uint4> &prog, const std::vector<float> &rays, i
                 ok = false; // the root must be the only list left on the pool stack
         }
         // generated code, first-hit flavour
-        ev.poolBase = 0, ev.cap = cap, ev.top = 0, ev.ovf = false;
+        ev.poolBase = 0, ev.cap = cap, ev.top = 0, ev.ovf = false, ev.tab = kTabTrace;
         float t = -1.f;
         uint32_t tag = 0u;
         const int kind = specTrace<O0>(ev, o, d, t, tag);
@@ -101,6 +108,9 @@ int main(int argc, char **argv)
         rays.insert(rays.end(), buf, buf + 6);
     if(f)
         fclose(f);
+    for(threadIdx.x = 0; threadIdx.x < PTB_FAST_THREADS; threadIdx.x++) // the CTA-wide staging loops of the two modules
+        ptb::specStageTable(kTabTrace), ptb::specStageTableList(kTabList);
+    threadIdx.x = 0;
     const int cap = atoi(argv[3]), maxStack = atoi(argv[5]);
     return atoi(argv[4]) ? run<true>(prog, rays, cap, maxStack) : run<false>(prog, rays, cap, maxStack);
 }
