@@ -12,6 +12,8 @@
 // through __ballot_sync/__popc warp-aggregated compaction so every store is coalesced.
 #include <cub/device/device_radix_sort.cuh>
 
+#include <stdlib.h>
+
 #include "ptb_launch.h"
 #include "ptb_trace.cuh"
 #include "ptb_shade.cuh"
@@ -23,7 +25,7 @@ namespace ptb
 // CTAs per SM the shade kernels are compiled for: camera hits are coherent and want registers (128),
 // bounce hits are scattered and want warps to hide their gathers (80 registers)
 #ifndef PTB_SHADE_MIN_CTAS
-#define PTB_SHADE_MIN_CTAS 4
+#define PTB_SHADE_MIN_CTAS 6 /* measured on B200, C5 primary shade per frame: 4 CTAs (128 registers) 245 ms, 5: 227, 6 (80 registers): 214 */
 #endif
 #ifndef PTB_SHADE_MIN_CTAS_BOUNCE
 #define PTB_SHADE_MIN_CTAS_BOUNCE 6
@@ -234,8 +236,8 @@ __device__ __forceinline__ bool shadeHitRecord(const DevScene &sc, const RenderP
 // PRIMARY: path state is regenerated from the sample index; otherwise it is read from `in`.
 // Survivors are appended to `out` with __ballot_sync/__popc warp aggregation (one atomic per warp,
 // coalesced stores).
-template <bool PRIMARY>
-__global__ void __launch_bounds__(PTB_SHADE_THREADS, PRIMARY ? PTB_SHADE_MIN_CTAS : PTB_SHADE_MIN_CTAS_BOUNCE) shadeKernel(DevScene sc, RenderPass pass, float4 *accum, const uint2 *__restrict__ hits, RayQueue in,
+template <bool PRIMARY, int MINCTAS = PRIMARY ? PTB_SHADE_MIN_CTAS : PTB_SHADE_MIN_CTAS_BOUNCE>
+__global__ void __launch_bounds__(PTB_SHADE_THREADS, MINCTAS) shadeKernel(DevScene sc, RenderPass pass, float4 *accum, const uint2 *__restrict__ hits, RayQueue in,
                                                                  const unsigned *__restrict__ inCount, RayQueue out, unsigned *outCount)
 {
     const unsigned nPix = (unsigned)pass.rw * (unsigned)pass.rh;
@@ -436,19 +438,56 @@ void launchTraceQueue(const DevScene &sc, const CsgConfig &cfg, RayQueue in, con
         traceQueueKernel<true><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, in, inCount, hits);
     }
 }
+// Resident CTAs per SM the shade kernels are compiled for, selectable for measurements: PTB_SHADE_CTAS (camera hits:
+// 4 = 128 registers, 6 = 80 (default), 7, 8 = 64) and PTB_SHADE_CTAS_BOUNCE (4, 6, 8).
+static int shadeVariant(bool primary)
+{
+    static const int p = getenv("PTB_SHADE_CTAS") ? atoi(getenv("PTB_SHADE_CTAS")) : PTB_SHADE_MIN_CTAS;
+    static const int b = getenv("PTB_SHADE_CTAS_BOUNCE") ? atoi(getenv("PTB_SHADE_CTAS_BOUNCE")) : PTB_SHADE_MIN_CTAS_BOUNCE;
+    return primary ? p : b;
+}
 void launchShade(const DevScene &sc, int blocks, bool primary, const RenderPass &pass, float4 *accum, const uint2 *hits, RayQueue in, const unsigned *inCount, RayQueue out,
                  unsigned *outCount, cudaStream_t stream)
 {
+    const int variant = shadeVariant(primary);
+#define PTB_SHADE_LAUNCH(P, C) shadeKernel<P, C><<<blocks, PTB_SHADE_THREADS, 0, stream>>>(sc, pass, accum, hits, in, inCount, out, outCount)
     if(primary)
-        shadeKernel<true><<<blocks, PTB_SHADE_THREADS, 0, stream>>>(sc, pass, accum, hits, in, inCount, out, outCount);
+    {
+        if(variant == 4)
+            PTB_SHADE_LAUNCH(true, 4);
+        else if(variant == 7)
+            PTB_SHADE_LAUNCH(true, 7);
+        else if(variant == 8)
+            PTB_SHADE_LAUNCH(true, 8);
+        else
+            PTB_SHADE_LAUNCH(true, PTB_SHADE_MIN_CTAS);
+    }
     else
-        shadeKernel<false><<<blocks, PTB_SHADE_THREADS, 0, stream>>>(sc, pass, accum, hits, in, inCount, out, outCount);
+    {
+        if(variant == 8)
+            PTB_SHADE_LAUNCH(false, 8);
+        else if(variant == 4)
+            PTB_SHADE_LAUNCH(false, 4);
+        else
+            PTB_SHADE_LAUNCH(false, PTB_SHADE_MIN_CTAS_BOUNCE);
+    }
+#undef PTB_SHADE_LAUNCH
 }
 int shadeBlocksPerSm(bool primary)
 {
     int n = 0;
-    if((primary ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<true>, PTB_SHADE_THREADS, 0)
-                : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<false>, PTB_SHADE_THREADS, 0)) != cudaSuccess)
+    const int variant = shadeVariant(primary);
+    cudaError_t e;
+    if(primary)
+        e = variant == 4 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<true, 4>, PTB_SHADE_THREADS, 0)
+            : variant == 7 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<true, 7>, PTB_SHADE_THREADS, 0)
+            : variant == 8 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<true, 8>, PTB_SHADE_THREADS, 0)
+                           : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<true, PTB_SHADE_MIN_CTAS>, PTB_SHADE_THREADS, 0);
+    else
+        e = variant == 8 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<false, 8>, PTB_SHADE_THREADS, 0)
+            : variant == 4 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<false, 4>, PTB_SHADE_THREADS, 0)
+                           : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, shadeKernel<false, PTB_SHADE_MIN_CTAS_BOUNCE>, PTB_SHADE_THREADS, 0);
+    if(e != cudaSuccess)
     {
         cudaGetLastError();
         return 0;
