@@ -14,8 +14,8 @@ import subprocess
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-CLASSES = [("trace_primary", ("ptbSpecTracePrimary", "tracePrimaryKernel")), ("shade_primary", ("shadeKernel<(bool)1>", "shadeKernel<1>")),
-           ("trace_bounce", ("ptbSpecTraceQueue", "traceQueueKernel")), ("shade_bounce", ("shadeKernel<(bool)0>", "shadeKernel<0>")),
+CLASSES = [("trace_primary", ("ptbSpecTracePrimary", "tracePrimaryKernel")), ("shade_primary", ("shadeKernel<(bool)1", "shadeKernel<1")),
+           ("trace_bounce", ("ptbSpecTraceQueue", "traceQueueKernel")), ("shade_bounce", ("shadeKernel<(bool)0", "shadeKernel<0")),
            ("intersect", ("ptbSpecIntersect", "intersectFastKernel"))]
 WANT = {
     "gpu__time_duration.sum": "ms_under_ncu", "launch__registers_per_thread": "registers", "smsp__inst_executed.sum": "warp_instructions",
