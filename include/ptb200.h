@@ -233,7 +233,11 @@ int ptb200_device_count(void);
 int ptb200_trim(void);
 
 /* Copies everything it needs (caller keeps its buffers); the scene lives on the CUDA device that
- * is current at the time of the call.  Validates the program (stack discipline, index ranges). */
+ * is current at the time of the call.  Validates the program (stack discipline, index ranges).
+ * Limits (PTB_EINVAL beyond them; the reference has none): at most 32767 primitives (boundary tags are 16 bits)
+ * and at most 32 pending operands on the evaluator's stack — a balanced tree of any size fits (unionArray,
+ * src/test.cpp:52-64, needs log2 n), a right-deep chain `new Union(a, new Union(b, ...))` of more than 32
+ * objects does not: build it left-deep or balanced (Union is the same set either way). */
 int ptb200_scene_create(const PtbSceneDesc *desc, PtbScene **out);
 void ptb200_scene_destroy(PtbScene *scene);
 /* Appends an image after create (texops may name images not yet uploaded at create time). */

@@ -4,6 +4,9 @@
 // same floats: radiance = mantissa * 179 * 2^(e-136) (reference src/image.cpp:306-314) and the
 // writer is its inverse with the same run-length layout (src/image.cpp:398-481), so an image
 // written here is byte-identical to one written by the reference from the same floats.
+// Said plainly: writeHDR / encodeChannel RESTATE the decisions of src/image.cpp:398-481 one for one (the
+// exponent as log(max)/log(2), the +1e-5 guard, runs of three or more, the 0x7F / 0x80 run bytes) — byte identity
+// with the reference's files leaves no freedom there; this is a restatement of one function, not a redesign.
 #include "ptb200_scene.hpp"
 
 #include <ctype.h>
