@@ -802,6 +802,18 @@ const SpecKernels *specializeGet(const std::string &source, int device, int mode
             e = it->second;
         else if(mode != SPEC_PEEK)
         {
+            // Bounded: a process that renders an endless stream of distinct scenes (an animation, one scene per frame)
+            // neither piles up cubins and loaded modules nor stacks compiles.  Past kMaxEntries programs new ones stay
+            // interpreted (entries are never evicted: a scene may be launching their kernels); a background compile is
+            // started only while no other one is running (every compile uses all host cores: --split-compile=0).
+            const size_t kMaxEntries = 64;
+            if(cache().size() >= kMaxEntries)
+            {
+                err = "specialised-kernel cache full (64 scene programs in this process)";
+                return nullptr;
+            }
+            if(mode == SPEC_START && g_inFlight > 0)
+                return nullptr; // try again at the next pass / call
             e = new Entry();
             cache()[source] = e;
             g_inFlight++;
