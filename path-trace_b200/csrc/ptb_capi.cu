@@ -894,13 +894,70 @@ int ptb::sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> 
     for(int i = 0; i < d->n_texops; i++)
         texops[i] = make_int2(d->texops[i].kind, d->texops[i].arg);
     std::vector<float> texdata(d->texdata, d->texdata + d->n_texdata);
+    // Fold the chains the materials start (DevTexBaked, ptb_scene_dev.cuh); validateTexture has bounded every chain.
+    std::vector<DevTexBaked> baked((size_t)std::max(1, d->n_texops));
+    memset(baked.data(), 0, baked.size() * sizeof(DevTexBaked));
+    for(int i = 0; i < d->n_materials; i++)
+        for(int k = 0; k < 5; k++)
+        {
+            const int root = d->materials[i].tex[k];
+            DevTexBaked b;
+            memset(&b, 0, sizeof(b));
+            uint32_t fl = PTB_TB_VALID;
+            bool ok = true, mapped = false;
+            int j = root;
+            for(; ok && !PTB_TEX_IS_LEAF(d->texops[j].kind); j++)
+            {
+                const PtbTexOp &op = d->texops[j];
+                if(op.kind == PTB_TEX_AFFINE)
+                {
+                    if((fl & PTB_TB_AFFINE) || mapped) // one matrix, above the map
+                        ok = false;
+                    const float *m = d->texdata + op.arg;
+                    b.r0 = make_float4(m[0], m[1], m[2], m[3]), b.r1 = make_float4(m[4], m[5], m[6], m[7]), b.r2 = make_float4(m[8], m[9], m[10], m[11]);
+                    fl |= PTB_TB_AFFINE;
+                }
+                else if(op.kind == PTB_TEX_MIRRORBALL || op.kind == PTB_TEX_SPHERICAL)
+                {
+                    if(mapped)
+                        ok = false;
+                    mapped = true;
+                    fl |= op.kind == PTB_TEX_SPHERICAL ? PTB_TB_SPHERICAL : PTB_TB_MIRRORBALL;
+                }
+                else if(op.kind == PTB_TEX_MULTIPLY)
+                {
+                    if(fl & PTB_TB_MUL)
+                        ok = false;
+                    const float *c = d->texdata + op.arg;
+                    b.mul = make_float4(c[0], c[1], c[2], 0.f);
+                    fl |= PTB_TB_MUL; // (a LogTexture met later lies BELOW this one and acts first)
+                }
+                else if(op.kind == PTB_TEX_LOG)
+                {
+                    if(fl & PTB_TB_LOG)
+                        ok = false;
+                    fl |= PTB_TB_LOG | ((fl & PTB_TB_MUL) ? PTB_TB_LOG_FIRST : 0u);
+                }
+                else
+                    ok = false;
+            }
+            const int leaf = d->texops[j].kind;
+            if(!ok || leaf == PTB_TEX_CONST)
+                continue; // (a bare ColorTexture is folded into the material record above)
+            if(leaf == PTB_TEX_SKYBOX || leaf == PTB_TEX_SKYBOX_ALPHA)
+                fl |= PTB_TB_SKYBOX;
+            if(leaf == PTB_TEX_IMAGE_ALPHA || leaf == PTB_TEX_SKYBOX_ALPHA)
+                fl |= PTB_TB_ALPHA;
+            b.flags = fl, b.image = d->texops[j].arg;
+            baked[root] = b;
+        }
 
     DevScene &dev = s->dev;
     memset(&dev, 0, sizeof(dev));
     int rc;
     if((rc = upload(s, prog, &dev.program)) || (rc = upload(s, fast, &dev.fastProgram)) || (rc = upload(s, geo, &dev.primGeo)) || (rc = upload(s, meta, &dev.primMeta)) ||
        (rc = upload(s, chainXf, &dev.chainXf)) || (rc = upload(s, xf, &dev.xforms)) || (rc = upload(s, mats, &dev.materials)) ||
-       (rc = upload(s, texops, &dev.texops)) || (rc = upload(s, texdata, &dev.texdata)))
+       (rc = upload(s, texops, &dev.texops)) || (rc = upload(s, texdata, &dev.texdata)) || (rc = upload(s, baked, &dev.texBaked)))
         return rc;
     dev.programWords = (int)prog.size();
     dev.fastWords = (int)fast.size();

@@ -190,8 +190,34 @@ __device__ __forceinline__ void accumulateWarp(float4 *accum, uint32_t pixel, V3
     const uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, pixel, 1);
     const bool head = lane == 0u || prev != pixel;
     const unsigned heads = __ballot_sync(0xFFFFFFFFu, head);
-    const unsigned after = lane == 31u ? 0xFFFFFFFFu : (heads >> (lane + 1u)) | (0xFFFFFFFFu << (31u - lane)); // bit k-1: lane + k starts a new run (or is past the warp)
     float x = rad.x, y = rad.y, z = rad.z, w = done;
+    if(heads == 0x00010001u || heads == 1u)
+    { // The usual case of the camera-ray level: 16 (or a multiple of 32) samples per pixel and pass, so the warp holds
+      // two aligned runs of 16 lanes (or one of 32).  Transposing butterfly: a lane gives away half of its values in
+      // each of the first two rounds (x, y against z, w across lanes 8 apart; then one of the two left across lanes
+      // 4 apart) and is left with ONE component summed over four lanes; two more rounds finish the sum over the 16
+      // lanes.  5 shuffles (6 for a run of 32) + 3 to collect the float4 instead of 20 (ncu: accumulateWarp and its
+      // shuffles were 78 of the 578 instructions of a camera-ray shade trip, profiles/r02k_full_c5.txt).
+        const bool up8 = (lane & 8u) != 0u, up4 = (lane & 4u) != 0u;
+        float k0 = up8 ? z : x, k1 = up8 ? w : y;
+        k0 += __shfl_xor_sync(0xFFFFFFFFu, up8 ? x : z, 8);
+        k1 += __shfl_xor_sync(0xFFFFFFFFu, up8 ? y : w, 8);
+        float v = (up4 ? k1 : k0) + __shfl_xor_sync(0xFFFFFFFFu, up4 ? k0 : k1, 4);
+        v += __shfl_xor_sync(0xFFFFFFFFu, v, 2);
+        v += __shfl_xor_sync(0xFFFFFFFFu, v, 1);
+        if(heads == 1u)
+            v += __shfl_xor_sync(0xFFFFFFFFu, v, 16);
+        // lanes 4c .. 4c+3 of each half now hold component c of that half's pixel
+        const unsigned half = lane & 16u;
+        const float sy = __shfl_sync(0xFFFFFFFFu, v, half + 4u), sz = __shfl_sync(0xFFFFFFFFu, v, half + 8u), sw = __shfl_sync(0xFFFFFFFFu, v, half + 12u);
+        if(head && pixel != 0xFFFFFFFFu && (v != 0.f || sy != 0.f || sz != 0.f || sw != 0.f))
+            atomicAdd(&accum[pixel], make_float4(v, sy, sz, sw));
+        return;
+    }
+    // Runs of any length (bounce levels: the queue holds what survived, in order): segmented sum down the lanes.  (The
+    // count of finished paths as a population count over the run instead of a fourth shuffled value executed as many
+    // instructions and put ballot -> ffs -> popc in series: shadeKernel<bounce> 1.16 -> 1.27 ms, profiles/r02m.)
+    const unsigned after = lane == 31u ? 0xFFFFFFFFu : (heads >> (lane + 1u)) | (0xFFFFFFFFu << (31u - lane)); // bit k-1: lane + k starts a new run (or is past the warp)
 #pragma unroll
     for(unsigned d = 1u; d < 32u; d <<= 1)
     {

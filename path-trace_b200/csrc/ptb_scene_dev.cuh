@@ -13,6 +13,29 @@ struct DevImage
     int w, h;
 };
 
+// A texture chain folded into one 80-byte record when the scene is created (five independent 16-byte loads instead of
+// the texops -> texdata -> texops ... chain of dependent ones, and no dispatch on op codes).  Chains of the form
+// [affine] [mirror-ball | spherical map] image-or-sky-box leaf, filtered by at most one MultiplyTexture and one
+// LogTexture in either order — every texture of the reference's scenes (src/test.cpp:93-105) — are folded; any
+// other chain has flags = 0 and runs through the interpreter (ptb_texture.cuh).  Indexed like texops (by chain root).
+#define PTB_TB_VALID 1u
+#define PTB_TB_AFFINE 2u
+#define PTB_TB_MIRRORBALL 4u
+#define PTB_TB_SPHERICAL 8u
+#define PTB_TB_SKYBOX 16u
+#define PTB_TB_ALPHA 32u
+#define PTB_TB_MUL 64u
+#define PTB_TB_LOG 128u
+#define PTB_TB_LOG_FIRST 256u /* the LogTexture lies below the MultiplyTexture: log first, then multiply */
+struct DevTexBaked
+{
+    uint32_t flags;
+    int image; // the leaf's image (the first of six for a sky box)
+    float pad0, pad1;
+    float4 r0, r1, r2; // rows of the TransformedTexture's matrix
+    float4 mul;        // the MultiplyTexture's factor
+};
+
 #define PTB_MAT_TERMINAL (1 << 8) /* constMask: a path ends on this material after the emission term (no refraction, zero reflectance) */
 struct DevMaterial
 {
@@ -36,6 +59,7 @@ struct DevScene
     const DevMaterial *materials;
     const int2 *texops;       // kind, arg
     const float *texdata;
+    const DevTexBaked *texBaked; // [n_texops]
     const DevImage *images;
     int nPrims, nMaterials, nTexops, nImages;
     const uint4 *fastProgram; // the same program compiled for the fast evaluator (ptb_csg_fast.cuh)

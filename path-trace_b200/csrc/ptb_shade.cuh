@@ -120,12 +120,33 @@ __device__ __forceinline__ bool shadeVertex(const DevScene &sc, PathState &ps, c
     const DevMaterial &m = sc.materials[hit.mat];
     V3 hitPos = Ar<false>::point(ps.o, ps.d, hit.t);
     const int cm = m.constMask; // bare ColorTextures were folded into the material record at scene create
-    V3 e = (cm & (1 << PTB_MAT_EMISSIVE)) ? mk(m.emissive.x, m.emissive.y, m.emissive.z) : texColor(sc, m.tex[PTB_MAT_EMISSIVE], hitPos, bilinear);
+    const bool ends = (cm & PTB_MAT_TERMINAL) || ps.depth == 0u || ps.strength < PTB_EPS; // path-trace.h:105-108; a terminal material's child carries weight 0 (:161)
+    // The material's five values at the hit point.  Slots that are not constants are evaluated here, in ONE loop
+    // around the texture evaluator (one copy of its code in the kernel); a vertex that ends the path only emits.
+    // Textures are pure functions of the position, so evaluating the reflectance before the refraction test
+    // (the reference asks for it after, path-trace.h:110-160) changes nothing.
+    V3 e = mk(m.emissive.x, m.emissive.y, m.emissive.z), refl = mk(m.reflect.x, m.reflect.y, m.reflect.z), tr = mk(m.transmit.x, m.transmit.y, m.transmit.z);
+    float trc = m.trcF, scat = m.scatterF;
+#pragma unroll 1
+    for(int need = ~cm & (ends ? (1 << PTB_MAT_EMISSIVE) : 31); need; need &= need - 1)
+    {
+        const int k = __ffs(need) - 1;
+        const float4 v = texEval(sc.texBaked, sc.texops, sc.texdata, sc.images, m.tex[k], hitPos.x, hitPos.y, hitPos.z, bilinear);
+        if(k == PTB_MAT_EMISSIVE)
+            e = mk(v.x, v.y, v.z);
+        else if(k == PTB_MAT_REFLECT)
+            refl = mk(v.x, v.y, v.z);
+        else if(k == PTB_MAT_TRANSMIT)
+            tr = mk(v.x, v.y, v.z);
+        else if(k == PTB_MAT_SCATTER)
+            scat = v.w;
+        else
+            trc = v.w;
+    }
     radiance.x += ps.thr.x * e.x, radiance.y += ps.thr.y * e.y, radiance.z += ps.thr.z * e.z;
-    if(ps.depth == 0u || ps.strength < PTB_EPS) // path-trace.h:105-108
+    if(ends)
         return false;
     float addFactor = 1.f;
-    float trc = (cm & (1 << PTB_MAT_TRC)) ? m.trcF : texFloat(sc, m.tex[PTB_MAT_TRC], hitPos, bilinear);
     trc = fmaxf(0.f, fminf(1.f, trc));
     float refractFactor = trc > 0.f ? trc * refractStrength(ps.d, hit.ior, hit.n) : 0.f;
     if(refractFactor > PTB_EPS) // path-trace.h:111-121
@@ -146,7 +167,6 @@ __device__ __forceinline__ bool shadeVertex(const DevScene &sc, PathState &ps, c
             }
             if(take)
             {
-                V3 tr = (cm & (1 << PTB_MAT_TRANSMIT)) ? mk(m.transmit.x, m.transmit.y, m.transmit.z) : texColor(sc, m.tex[PTB_MAT_TRANSMIT], hitPos, bilinear);
                 ps.strength = ps.strength * refractFactor * addFactor * Ar<false>::length(tr);
                 ps.thr = mk(ps.thr.x * tr.x * w, ps.thr.y * tr.y * w, ps.thr.z * tr.z * w);
                 ps.o = hitPos, ps.d = rd;
@@ -159,12 +179,10 @@ __device__ __forceinline__ bool shadeVertex(const DevScene &sc, PathState &ps, c
     if(addFactor < PTB_EPS)
         return false;
     // diffuse / specular reflection, path-trace.h:127-163
-    float scat = (cm & (1 << PTB_MAT_SCATTER)) ? m.scatterF : texFloat(sc, m.tex[PTB_MAT_SCATTER], hitPos, bilinear);
     scat = fmaxf(0.f, fminf(1.f, scat));
     int count = (int)(10000.f * ps.strength * addFactor * scat);
     if(scat <= PTB_EPS || count == 0)
         count = 1;
-    V3 refl = (cm & (1 << PTB_MAT_REFLECT)) ? mk(m.reflect.x, m.reflect.y, m.reflect.z) : texColor(sc, m.tex[PTB_MAT_REFLECT], hitPos, bilinear);
     if(isZero(refl)) // zero-weight child: contributes exactly 0, not traced
         return false;
     V3 nd = vreflect(ps.d, hit.n);

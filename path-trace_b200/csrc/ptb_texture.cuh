@@ -96,27 +96,51 @@ __device__ __forceinline__ V3 texSpherical(V3 p) // include/transform_texture.h:
     return mk(fmaf(theta, 0.15915494309189535f, 0.5f), fmaf(phi, 0.3183098861837907f, 0.5f), 0.f);
 }
 
-// Evaluates texture chain `root` at pos.  wantFloat selects Texture::getFloat semantics:
-// position wrappers forward getFloat (texture.h:78-81, transform_texture.h:30-33), filters do
-// not override it, so under a filter the chain runs as getColor and the mean is taken above.
-__device__ __forceinline__ void evalTexture(const DevScene &sc, int root, V3 pos, bool wantFloat, bool bilinear, V3 &color, float &f)
+// One texture chain at one position: rgb in xyz, Texture::getFloat in w.  Inlined ONCE per kernel: shadeVertex
+// evaluates the material slots that need it in a loop around this function.  (Inlined at each of the five slots the
+// interpreter below made the shade kernels 6 600 instructions long and 9 % of their stall samples instruction
+// fetches, profiles/r02k_full_c5.txt; as an out-of-line function the call spilled the path state around it and the
+// camera-ray shade kernel lost what it had won, profiles/r02n.)
+//
+// Folded chains (DevTexBaked, ptb_scene_dev.cuh) run straight through; the rest are interpreted: position wrappers
+// forward getFloat (texture.h:78-81, transform_texture.h:30-33), filters do not override it, so under a filter the
+// chain runs as getColor and the mean is taken above.
+__device__ __forceinline__ float4 texEval(const DevTexBaked *__restrict__ baked, const int2 *__restrict__ texops, const float *__restrict__ texdata,
+                                          const DevImage *__restrict__ images, int root, float x, float y, float z, bool bilinear)
 {
-    int i = root;
-    int2 op = __ldg(&sc.texops[i]);
-    // fast path: a bare ColorTexture (every material slot of the default materials)
-    if(op.x == PTB_TEX_CONST)
+    V3 pos = mk(x, y, z), color;
+    float f;
+    const float4 *rec = reinterpret_cast<const float4 *>(baked + root);
+    const float4 head = __ldg(rec), r0 = __ldg(rec + 1), r1 = __ldg(rec + 2), r2 = __ldg(rec + 3), mul = __ldg(rec + 4); // (all five at once)
+    const uint32_t fl = __float_as_uint(head.x);
+    if(fl & PTB_TB_VALID)
     {
-        const float *d = sc.texdata + op.y;
-        color = mk(__ldg(d), __ldg(d + 1), __ldg(d + 2));
-        f = meanRgb(color);
-        return;
+        const DevImage *im = images + __float_as_int(head.y);
+        if(fl & PTB_TB_AFFINE) // TransformedTexture, include/texture.h:74-81
+            pos = Ar<true>::apply(r0, r1, r2, pos);
+        if(fl & PTB_TB_SPHERICAL)
+            pos = texSpherical(pos);
+        else if(fl & PTB_TB_MIRRORBALL)
+            pos = texMirrorBall(pos);
+        const float4 px = (fl & PTB_TB_SKYBOX) ? skyboxLookup(im, pos, bilinear) : imageLookup(*im, pos, bilinear);
+        color = (fl & PTB_TB_ALPHA) ? mk(px.w, px.w, px.w) : mk(px.x, px.y, px.z); // include/image_texture.h:45-66,135-176
+        if(fl & PTB_TB_LOG_FIRST)
+            color = mk(texLog(color.x), texLog(color.y), texLog(color.z));
+        if(fl & PTB_TB_MUL) // include/filter_texture.h:43-46
+            color = mk(color.x * mul.x, color.y * mul.y, color.z * mul.z);
+        if((fl & (PTB_TB_LOG | PTB_TB_LOG_FIRST)) == PTB_TB_LOG) // include/filter_texture.h:68-71
+            color = mk(texLog(color.x), texLog(color.y), texLog(color.z));
+        f = (fl & PTB_TB_ALPHA) && !(fl & (PTB_TB_MUL | PTB_TB_LOG)) ? px.w : meanRgb(color);
+        return make_float4(color.x, color.y, color.z, f);
     }
+    int i = root;
+    int2 op = __ldg(&texops[i]);
     bool filtered = false;
     while(!PTB_TEX_IS_LEAF(op.x))
     {
         if(op.x == PTB_TEX_AFFINE) // TransformedTexture, include/texture.h:74-81
         {
-            const float *m = sc.texdata + op.y;
+            const float *m = texdata + op.y;
             float4 r0 = make_float4(__ldg(m), __ldg(m + 1), __ldg(m + 2), __ldg(m + 3));
             float4 r1 = make_float4(__ldg(m + 4), __ldg(m + 5), __ldg(m + 6), __ldg(m + 7));
             float4 r2 = make_float4(__ldg(m + 8), __ldg(m + 9), __ldg(m + 10), __ldg(m + 11));
@@ -128,23 +152,23 @@ __device__ __forceinline__ void evalTexture(const DevScene &sc, int root, V3 pos
             pos = texSpherical(pos);
         else
             filtered = true;
-        op = __ldg(&sc.texops[++i]);
+        op = __ldg(&texops[++i]);
     }
     float4 px;
     bool alpha = false;
     if(op.x == PTB_TEX_CONST)
     {
-        const float *d = sc.texdata + op.y;
+        const float *d = texdata + op.y;
         px = make_float4(__ldg(d), __ldg(d + 1), __ldg(d + 2), 0.f);
     }
     else if(op.x == PTB_TEX_IMAGE || op.x == PTB_TEX_IMAGE_ALPHA)
     {
-        px = imageLookup(sc.images[op.y], pos, bilinear);
+        px = imageLookup(images[op.y], pos, bilinear);
         alpha = op.x == PTB_TEX_IMAGE_ALPHA;
     }
     else
     {
-        px = skyboxLookup(sc.images + op.y, pos, bilinear);
+        px = skyboxLookup(images + op.y, pos, bilinear);
         alpha = op.x == PTB_TEX_SKYBOX_ALPHA;
     }
     if(alpha) // getColor = Color(alpha), getFloat = alpha (include/image_texture.h:45-66,135-176)
@@ -157,20 +181,30 @@ __device__ __forceinline__ void evalTexture(const DevScene &sc, int root, V3 pos
         color = mk(px.x, px.y, px.z);
         f = meanRgb(color);
     }
-    if(!filtered)
-        return;
-    for(int k = i - 1; k >= root; k--)
+    if(filtered)
     {
-        int2 w = __ldg(&sc.texops[k]);
-        if(w.x == PTB_TEX_MULTIPLY) // include/filter_texture.h:43-46
+        for(int k = i - 1; k >= root; k--)
         {
-            const float *d = sc.texdata + w.y;
-            color = mk(color.x * __ldg(d), color.y * __ldg(d + 1), color.z * __ldg(d + 2));
+            int2 w = __ldg(&texops[k]);
+            if(w.x == PTB_TEX_MULTIPLY) // include/filter_texture.h:43-46
+            {
+                const float *d = texdata + w.y;
+                color = mk(color.x * __ldg(d), color.y * __ldg(d + 1), color.z * __ldg(d + 2));
+            }
+            else if(w.x == PTB_TEX_LOG) // include/filter_texture.h:68-71
+                color = mk(texLog(color.x), texLog(color.y), texLog(color.z));
         }
-        else if(w.x == PTB_TEX_LOG) // include/filter_texture.h:68-71
-            color = mk(texLog(color.x), texLog(color.y), texLog(color.z));
+        f = meanRgb(color);
     }
-    f = meanRgb(color);
+    return make_float4(color.x, color.y, color.z, f);
+}
+
+// Evaluates texture chain `root` at pos: colour (Texture::getColor) and float (Texture::getFloat) values.
+__device__ __forceinline__ void evalTexture(const DevScene &sc, int root, V3 pos, bool wantFloat, bool bilinear, V3 &color, float &f)
+{
+    (void)wantFloat;
+    const float4 v = texEval(sc.texBaked, sc.texops, sc.texdata, sc.images, root, pos.x, pos.y, pos.z, bilinear);
+    color = mk(v.x, v.y, v.z), f = v.w;
 }
 
 __device__ __forceinline__ V3 texColor(const DevScene &sc, int root, V3 pos, bool bilinear)

@@ -27,22 +27,28 @@ def test_generated_source_compiles_for_sm100a():
         assert ("specTrace" if which == 0 else "specList") in source and "rlUnionInto(ev, " in source and "ptb_csg_reg.cuh" in source
         assert ("ptbSpecTracePrimary" in source) == (which == 0) and ("ptbSpecIntersectO0" in source) == (which == 1)
         assert cubin > 10000
-    # every leaf of the tree has its code
+    # every leaf of the tree has its code: the eight isomorphic groups of config 4 (six transformed spheres cut by
+    # two planes) share ONE out-of-line function that reads its constants from the module's table, called per group
+    import re
     flat = device.Flat(scenes.config4(b))
     source, _ = device.specialize_probe(flat, 0, compile=False)
-    assert source.count("xfDisc<O0>") >= 48 and source.count("planeFold<O0>") >= 22
+    calls = len(re.findall(r"= ptbShape0<O0>\(ev\.poolBase", source))
+    assert calls == 8 and source.count("xfDisc<O0>") == 6 and "ldsTab128" in source
+    assert calls * 6 >= 48 and (source.count("planeFold<O0>") - 2) + calls * 2 >= 22
 
 
-def test_sphere_runs_are_marked_in_the_compiled_stream():
+def test_sphere_runs_are_marked_in_the_compiled_stream(monkeypatch):
     """compileFastProgram flags the first leaf of every complete Union subtree of transformed spheres
     (FH_RUN, bit 30 of a header without tail, run length in bits 12-15): the eight groups of six
-    spheres of config 4; config 5 (untransformed spheres in a mixed tree) has none."""
+    spheres of config 4; config 5 (untransformed spheres in a mixed tree) has none.  (Read off the generated source
+    with every leaf written out in line: no shape functions.)"""
     import re
+    monkeypatch.setenv("PTB_SPEC_SHAPES", "0")
     b = product_builder()
 
     def run_headers(world):
         source, _ = device.specialize_probe(device.Flat(world), 0, compile=False)
-        heads = [int(h, 16) for h in re.findall(r"xfDisc<O0>\(make_uint4\((0x[0-9a-f]{8})u", source)]
+        heads = [int(h, 16) for h in re.findall(r"const uint4 k0 = make_uint4\((0x[0-9a-f]{8})u[^\n]*\n\s*xfDisc<O0>\(k0, ", source)]
         return [(h >> 12) & 15 for h in heads if (h & 0x40000080) == 0x40000000]
 
     assert run_headers(scenes.config4(b)) == [6] * 8
