@@ -414,6 +414,11 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
         memcpy(&u, &f, 4);
         return u;
     };
+    auto u2f = [](uint32_t u) {
+        float f;
+        memcpy(&f, &u, 4);
+        return (double)f;
+    };
     std::vector<FastItem> seq;
     for(int i = 0; i < d->n_ops; i++)
     {
@@ -662,6 +667,7 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
         if(allUnion)
             out[w].x |= FH_UNION_TAIL;
     }
+    std::vector<size_t> runs; // header word of every run's first leaf
     { // Sphere runs: a complete Union-only subtree of 3..15 transformed spheres whose records are adjacent and
       // which no operator follows directly (it is a left operand, or the root).  If no ray of a warp of CAMERA
       // rays hits any of them, all the subtree does is push one empty list: the evaluator tests the run's
@@ -703,7 +709,10 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
                 if(seq[k].kind == PTB_OP_PUSH_PRIM)
                     adjacent = leafWord[k] == leafWord[f] + 4u * (size_t)leaf++;
             if(adjacent)
+            {
                 out[leafWord[f]].x |= FH_RUN | ((uint32_t)n << 12);
+                runs.push_back(leafWord[f]);
+            }
         }
     }
     for(size_t w = 0; w < out.size();)
@@ -715,6 +724,76 @@ static void compileFastProgram(const PtbSceneDesc *d, std::vector<uint4> &out, i
         }
         else
             w += recordLength(w);
+    }
+    { // Bounding spheres of the runs' leaves, behind FK_END (the evaluators never run into them; a run's first header
+      // carries their word index in bits 16-29).  A leaf is {x : |M x + t'|^2 <= r^2}: an ellipsoid centred at
+      // C = -M^-1 t' that lies within R = r / sigma_min(M) of C.  Used by camera rays only (origin 0): a word is
+      // {C, sqrt(|C|^2 - R^2)}.  PTB_FAST_BOUNDS=0 leaves them out.
+        const char *e = getenv("PTB_FAST_BOUNDS");
+        const bool enabled = !e || atoi(e) != 0;
+        for(size_t at = 0; enabled && at < runs.size(); at++)
+        {
+            const size_t w = runs[at];
+            const uint32_t n = (out[w].x >> 12) & 15u;
+            const size_t table = out.size();
+            if(table + n > 0x3FFFu)
+                break;
+            std::vector<uint4> words;
+            for(uint32_t k = 0; k < n; k++)
+            {
+                const uint4 *rec = &out[w + 4u * k];
+                double A[3][3], t[3], B[3][3];
+                for(int r = 0; r < 3; r++)
+                {
+                    A[r][0] = u2f(rec[1 + r].x), A[r][1] = u2f(rec[1 + r].y), A[r][2] = u2f(rec[1 + r].z), t[r] = u2f(rec[1 + r].w);
+                }
+                const double det = A[0][0] * (A[1][1] * A[2][2] - A[1][2] * A[2][1]) - A[0][1] * (A[1][0] * A[2][2] - A[1][2] * A[2][0]) +
+                                   A[0][2] * (A[1][0] * A[2][1] - A[1][1] * A[2][0]);
+                const double r2 = -(double)u2f(rec[0].z);
+                if(!(fabs(det) > 1e-12) || !(r2 > 0))
+                    break;
+                for(int i = 0; i < 3; i++)
+                    for(int j = 0; j < 3; j++)
+                    { // adjugate / det
+                        const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+                        B[j][i] = (A[i1][j1] * A[i2][j2] - A[i1][j2] * A[i2][j1]) / det;
+                    }
+                double C[3];
+                for(int i = 0; i < 3; i++)
+                    C[i] = -(B[i][0] * t[0] + B[i][1] * t[1] + B[i][2] * t[2]);
+                // sigma_max(B)^2 = largest eigenvalue of S = B^T B: power iteration from each axis (one of them has a
+                // component of at least 1/sqrt 3 along the leading eigenvector), the result rounded up; the trace
+                // bounds it from above.
+                double S[3][3], lambda = 0;
+                for(int i = 0; i < 3; i++)
+                    for(int j = 0; j < 3; j++)
+                        S[i][j] = B[0][i] * B[0][j] + B[1][i] * B[1][j] + B[2][i] * B[2][j];
+                for(int start = 0; start < 3; start++)
+                {
+                    double v[3] = {start == 0 ? 1.0 : 0.0, start == 1 ? 1.0 : 0.0, start == 2 ? 1.0 : 0.0}, len = 0;
+                    for(int it = 0; it < 200; it++)
+                    {
+                        double u[3] = {S[0][0] * v[0] + S[0][1] * v[1] + S[0][2] * v[2], S[1][0] * v[0] + S[1][1] * v[1] + S[1][2] * v[2], S[2][0] * v[0] + S[2][1] * v[1] + S[2][2] * v[2]};
+                        len = sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+                        if(!(len > 0))
+                            break;
+                        v[0] = u[0] / len, v[1] = u[1] / len, v[2] = u[2] / len;
+                    }
+                    lambda = std::max(lambda, len);
+                }
+                const double trace = S[0][0] + S[1][1] + S[2][2];
+                const double sigma2 = std::min(trace, lambda * 1.01);
+                const double R2 = r2 * sigma2 * 1.002 + 1e-9;
+                // the word: C and sqrt(|C|^2 - R^2) rounded down by a relative 1e-5 (far more than the rounding of the
+                // three-term dot product it is compared with); 0 when the origin lies inside: every line meets it
+                const double K = C[0] * C[0] + C[1] * C[1] + C[2] * C[2] - R2;
+                words.push_back(make_uint4(f2u((float)C[0]), f2u((float)C[1]), f2u((float)C[2]), f2u((float)(K > 0 ? sqrt(K) * (1.0 - 1e-5) : 0.0))));
+            }
+            if(words.size() != n)
+                continue; // a singular matrix: this run keeps the plain discriminant loop
+            out.insert(out.end(), words.begin(), words.end());
+            out[w].x |= (uint32_t)table << 16;
+        }
     }
 }
 

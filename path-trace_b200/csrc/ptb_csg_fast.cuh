@@ -58,7 +58,8 @@ enum
     FH_MISS_SHIFT = 1 << 6,
     FH_TAIL = 1 << 7,
     FH_UNION_TAIL = 1 << 30, // every operator of the tail is a Union (and the action is not Intersection)
-    FH_RUN = 1 << 30,        // SPHERE_XF WITHOUT a tail: first of a run of (x >> 12) & 15 adjacent leaves forming a whole Union subtree
+    FH_RUN = 1 << 30,        // SPHERE_XF WITHOUT a tail: first of a run of (x >> 12) & 15 adjacent leaves forming a whole Union subtree;
+                             // bits 16-29: word index of the run's bounding spheres {C.xyz, R^2}, one word a leaf, behind FK_END (0: none)
     FH_PAIR = 1u << 31       // SPHERE_XF without tail directly followed by another SPHERE_XF leaf
 };
 enum
@@ -470,6 +471,7 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
     for(int r = 0; r < R; r++)
         st[r].bits = 0u, st[r].top = 0, st[r].sp = c.stk + (uint32_t)r * c.stkStride;
     uint32_t pc = GP ? 0u : c.prog; // GP: word index; else shared byte address
+    uint32_t boundMask = 0u;        // warp-uniform: which of the coming leaves of a sphere run can be hit (> 1: inside a run)
 #define PTB_PROG(i) (GP ? __ldg(gprog + pc + (i)) : lds128(pc + 16u * (i)))
 #define PTB_ADVANCE(n) (pc += GP ? (uint32_t)(n) : 16u * (uint32_t)(n))
 // The commonest trips by far, taken by the whole warp together (votes), so that the loop stays
@@ -512,7 +514,48 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
             ltags[r] = h.y; // (the rest is set by the branch that sets hit[r]; two[r], ut0[r], utags[r] by planes only)
         if(h.x & FK_SPHERE_XF)
         {
-            if(O0 && (h.x & (FH_RUN | FH_TAIL)) == FH_RUN)
+            bool skipLeaf = false; // warp-uniform: no ray's line meets this leaf's bounding sphere
+            if(O0 && (h.x & (FH_RUN | FH_TAIL)) == FH_RUN && ((h.x >> 16) & 0x3FFFu) != 0u)
+            { // Camera rays, first leaf of a run whose world-space bounding spheres follow the program
+              // (compileFastProgram): one 16-byte word and 7 instructions per leaf instead of four words and ~32
+              // decide which leaves some ray of the warp can hit at all.  A line through the origin along d meets the
+              // sphere (C, R) iff (C.d)^2 >= |d|^2 (|C|^2 - R^2); the word holds C and sqrt(|C|^2 - R^2), rounded
+              // down.  A line that misses a leaf's bounding sphere misses the leaf, at any t: skipping it is treating
+              // it as the miss it is.  (ncu, C4: the 48 spheres cost 1 530 of a camera ray's 3 220 instructions to find
+              // that the warp's two pixels see one or none of them, profiles/r02k_full_c4.txt.  For queued rays — 32
+              // unrelated rays a warp, any origin — the vote seldom frees a leaf and the test costs what it saves.)
+                const uint32_t n = (h.x >> 12) & 15u, bi = (h.x >> 16) & 0x3FFFu;
+                float sd[R];
+                uint32_t met[R];
+#pragma unroll
+                for(int r = 0; r < R; r++)
+                    sd[r] = Ar<false>::sqrt(fmaf(d[r].x, d[r].x, fmaf(d[r].y, d[r].y, d[r].z * d[r].z))), met[r] = 0u;
+                for(uint32_t k = 0; k < n; k++)
+                {
+                    const uint4 bw = GP ? __ldg(gprog + bi + k) : lds128(c.prog + 16u * (bi + k));
+#pragma unroll
+                    for(int r = 0; r < R; r++)
+                    {
+                        const float bb = fmaf(__uint_as_float(bw.x), d[r].x, fmaf(__uint_as_float(bw.y), d[r].y, __uint_as_float(bw.z) * d[r].z));
+                        met[r] |= fabsf(bb) >= sd[r] * __uint_as_float(bw.w) ? 1u << k : 0u;
+                    }
+                }
+                uint32_t mask = 0u;
+#pragma unroll
+                for(int r = 0; r < R; r++)
+                    mask |= met[r];
+                mask = __reduce_or_sync(0xFFFFFFFFu, mask);
+                if(mask == 0u)
+                { // no leaf can be hit: the subtree is one empty list
+#pragma unroll
+                    for(int r = 0; r < R; r++)
+                        st[r].bits <<= 1;
+                    PTB_ADVANCE(4u * n);
+                    continue;
+                }
+                boundMask = mask | (1u << n); // bit k: leaf k of the run may be hit; the top bit marks the end
+            }
+            else if(O0 && (h.x & (FH_RUN | FH_TAIL)) == FH_RUN)
             { // camera rays: the whole Union subtree of spheres in one loop and one vote (see compileFastProgram).
               // ncu, C4: a leaf costs ~49 instructions one by one, 17 of them arithmetic; ~26 here.
                 const uint32_t n = (h.x >> 12) & 15u;
@@ -537,12 +580,21 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
                     continue;
                 }
             }
-            const uint4 u0 = PTB_PROG(1), u1 = PTB_PROG(2), u2 = PTB_PROG(3);
+            if(boundMask > 1u)
+                skipLeaf = !(boundMask & 1u), boundMask >>= 1;
             float a[R], b[R], e[R];
-            if(h.x & FH_PAIR)
+            if(skipLeaf)
+            {
+#pragma unroll
+                for(int r = 0; r < R; r++)
+                    a[r] = 1.f, b[r] = 0.f, e[r] = -1.f;
+                PTB_ADVANCE(4);
+            }
+            else if((h.x & FH_PAIR) && boundMask <= 1u)
             { // the next word is a transformed sphere too and this one has no tail: both discriminants
               // are computed together (ILP).  If no ray of the warp hits the first, it is done with and
               // the second becomes the leaf of this trip; otherwise the second waits for the next trip.
+                const uint4 u0 = PTB_PROG(1), u1 = PTB_PROG(2), u2 = PTB_PROG(3);
                 const uint4 g = PTB_PROG(4), v0 = PTB_PROG(5), v1 = PTB_PROG(6), v2 = PTB_PROG(7);
                 float a1[R], b1[R], e1[R];
                 bool any = false;
@@ -569,6 +621,7 @@ __device__ __forceinline__ void evalFast(const FastCtx &c, const uint4 *__restri
             }
             else
             {
+                const uint4 u0 = PTB_PROG(1), u1 = PTB_PROG(2), u2 = PTB_PROG(3);
 #pragma unroll
                 for(int r = 0; r < R; r++)
                     xfDisc<O0>(h, u0, u1, u2, o[r], d[r], a[r], b[r], e[r]);

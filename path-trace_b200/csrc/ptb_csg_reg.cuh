@@ -408,13 +408,23 @@ __device__ __forceinline__ int rlUnionFirstHit(const REval &ev, const RList &A, 
             k = rlScanSpan(b1, t, tag);
         return k < 0 ? PTB_HIT_MISS : k;
     }
-    int ia = 0, ib = 0;
+    int ia = 1, ib = 0;
     bool aEnded = false, bEnded = nB == 0;
-    SpanRec sa = A.a, sb = b0;
-    if(!aEnded)
-        sa = rlGet(ev, A, 0), ia = 1;
+    SpanRec sa = rlGet(ev, A, 0), sb = b0;
     if(!bEnded)
+    {
         ib = 1;
+        // B's first span ends behind the origin and before A begins — the lower span of a sky box seen from inside,
+        // src/test.cpp:134-140 — so the machine below would emit it first (:104-107) and the scan would pass over
+        // it: drop it here.
+        if(b0.t0 < PTB_EPS && b0.t1 < PTB_EPS && !(sa.t1 < b0.t0) && b0.t1 < sa.t0)
+        {
+            if(nB >= 2)
+                sb = b1, ib = 2;
+            else
+                bEnded = true;
+        }
+    }
     for(;;)
     {
         bool fromB; // which operand's current span goes out next, in the order of the reference's tests
@@ -430,8 +440,20 @@ __device__ __forceinline__ int rlUnionFirstHit(const REval &ev, const RList &A, 
             fromB = true; // :104-107
         else
         {
-            if(sa.t0 < sb.t0)
-            { // they overlap and A starts first: A absorbs B (:113-123)
+            // They overlap.  The span that starts first absorbs the other and from then on only its END moves (B is a
+            // leaf's or a cluster's list: in order; when B absorbs, no further span of A may be left to take over),
+            // so when it starts at or beyond eps the scan's answer is known now: the merged span's start.
+            const bool aFirst = sa.t0 < sb.t0;
+            const float w0 = aFirst ? sa.t0 : sb.t0;
+            if(w0 >= PTB_EPS && (aFirst || ia >= A.n))
+            {
+                if(w0 >= PTB_MAX_VALUE)
+                    return PTB_HIT_MISS;
+                t = w0, tag = (aFirst ? sa.tags : sb.tags) & 0xFFFFu; // startTag
+                return PTB_HIT_ENTER;
+            }
+            if(aFirst)
+            { // A absorbs B (:113-123)
                 if(sa.t1 < sb.t1)
                     copyEndFromEnd(sa, sb);
                 if(ib < nB)

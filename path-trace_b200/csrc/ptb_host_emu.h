@@ -52,6 +52,7 @@ static inline int __popc(uint32_t v) { return __builtin_popcount(v); }
 static inline bool __any_sync(unsigned, bool p) { return p; }
 static inline bool __all_sync(unsigned, bool p) { return p; }
 static inline unsigned __ballot_sync(unsigned, bool p) { return p ? 1u : 0u; }
+static inline unsigned __reduce_or_sync(unsigned, unsigned v) { return v; }
 static inline void __syncthreads() {}
 static inline void __syncwarp() {}
 template <class T> static inline T __ldg(const T *p) { return *p; }

@@ -137,3 +137,43 @@ def test_background_compile_switches_over_without_changing_the_image():
     assert scene.specialized()[2] == scene.specialized()[3] > 0
     np.testing.assert_allclose(img, ref, rtol=2e-5, atol=1e-6)
     np.testing.assert_allclose(img2, ref, rtol=2e-5, atol=1e-6)
+
+
+def test_run_bounding_spheres_enclose_their_leaves():
+    """Behind FK_END the compiled stream carries one bounding sphere per leaf of every sphere run (bits 16-29 of the
+    run's first header: word index), as {C, sqrt(|C|^2 - R^2)}: what the camera-ray test needs.  Every point of a
+    leaf {x : |M x + t'|^2 <= r^2} must lie inside its sphere — the interpreter skips a leaf whose sphere no ray of
+    the warp meets — and the spheres must not be slack by more than a few per cent of the leaf's longest half-axis."""
+    b = product_builder()
+    text, _ = device.specialize_probe(device.Flat(scenes.config4(b)), 2, compile=False)
+    words = np.array([int(w, 16) for w in text.split()], np.uint32).reshape(-1, 4)
+    as_f = lambda u: np.array(u, np.uint32).view(np.float32).astype(np.float64)
+    rs = np.random.RandomState(3)
+    u = rs.normal(size=(4000, 3))
+    u /= np.linalg.norm(u, axis=1, keepdims=True)
+    runs = 0
+    w = 0
+    while (words[w, 0] & 0x3F) != 8:  # FK_END
+        x = int(words[w, 0])
+        if x & 1:  # FK_SPHERE_XF: header + 3 rows
+            if (x & 0x40000080) == 0x40000000 and (x >> 16) & 0x3FFF:
+                runs += 1
+                n, table = (x >> 12) & 15, (x >> 16) & 0x3FFF
+                for k in range(n):
+                    rec = words[w + 4 * k:w + 4 * k + 4]
+                    rows = as_f(rec[1:4].reshape(-1)).reshape(3, 4)
+                    m, t, r = rows[:, :3], rows[:, 3], np.sqrt(-as_f(rec[0, 2:3])[0])
+                    c = as_f(words[table + k, :3])
+                    big_r = np.sqrt(c @ c - (as_f(words[table + k, 3:4])[0] / (1 - 1e-5)) ** 2)
+                    surface = np.linalg.solve(m, (r * u - t).T).T
+                    dist = np.linalg.norm(surface - c, axis=1)
+                    assert dist.max() <= big_r, (w, k)
+                    assert big_r <= 1.02 * r / np.linalg.svd(m, compute_uv=False).min() + 1e-4, (w, k)
+            w += 4
+        elif x & 2:
+            w += 2 + 2 * int(words[w, 2])
+        elif x & 4:
+            w += 2
+        else:
+            w += 1
+    assert runs == 8
