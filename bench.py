@@ -222,7 +222,7 @@ def load_json(*path):
         return {}
 
 
-def kernel_rooflines(name, desc, st, n_pix, passes, fp32_peak_tflops, hbm_peak_gbs, spec_all):
+def kernel_rooflines(name, desc, st, n_pix, passes, fp32_peak_tflops, hbm_peak_gbs, spec_all, camera_only=False):
     """One roofline entry per kernel class of the wavefront, from the CUDA-event times the library
     took around every launch of the instrumented step (PtbStats).  Trace kernels: FP32 issue bound,
     trace-only flops.  Shade kernels: HBM bound, algorithmic bytes:
@@ -244,7 +244,7 @@ def kernel_rooflines(name, desc, st, n_pix, passes, fp32_peak_tflops, hbm_peak_g
         ("trace_primary", spec, "fp32", st.ms_trace_primary, st.rays_primary, st.rays_primary * (fpr + CAMERA_FLOPS), "%d flop/ray (model %d + camera %d)" % (fpr + CAMERA_FLOPS, fpr, CAMERA_FLOPS)),
         ("shade_primary", "shadeKernel<primary>", "hbm", st.ms_shade_primary, st.rays_primary,
          8.0 * st.rays_primary + 64.0 * st.rays_first_bounce + 32.0 * n_pix * passes, "8 B/path + 64 B/survivor + 32 B/pixel/pass"),
-        ("trace_bounce", "ptbSpecTraceQueue (scene-specialised, NVRTC)" if spec_all and os.environ.get("PTB_SPEC_BOUNCE", "1") != "0" else "traceQueueKernel (interpreter)", "fp32", st.ms_trace_bounce, st.rays_bounce, st.rays_bounce * fpr, "%d flop/ray" % fpr),
+        ("trace_bounce", "ptbSpecTraceQueue (scene-specialised, NVRTC)" if spec_all and not camera_only and os.environ.get("PTB_SPEC_BOUNCE", "1") != "0" else "traceQueueKernel (interpreter)", "fp32", st.ms_trace_bounce, st.rays_bounce, st.rays_bounce * fpr, "%d flop/ray" % fpr),
         ("shade_bounce", "shadeKernel<bounce>", "hbm", st.ms_shade_bounce, st.rays_bounce,
          72.0 * st.rays_bounce + 64.0 * survivors_bounce + 32.0 * finished_bounce, "72 B/ray + 64 B/survivor + 32 B/finished path"),
     ]
@@ -280,6 +280,16 @@ def run_render(scene, flat, name, width, height, spp, steps, warmup, samples_per
     for _ in range(warmup):
         step(False)
     torch.cuda.synchronize()
+    if warmup > 0 and os.environ.get("PTB_SPECIALIZE", "") != "0":
+        # a scene-specialised kernel the library decided to compile (NVRTC, background thread): a one-time cost, like
+        # any JIT warm-up — wait for it and run one more untimed frame
+        deadline, waited = time.time() + 90, False
+        while not scene.specialized()[0] and scene.spec_pending and time.time() < deadline:
+            time.sleep(0.05)
+            waited = True
+        if waited:
+            step(False)
+            torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for _ in range(steps):
@@ -441,12 +451,14 @@ def run_ours(args):
     # The scene-specialised trace kernels are compiled (NVRTC, 1-2 s, once per process and scene program) on a
     # background thread while the first frames run interpreted; with N GPUs the warm-up frames are N times shorter,
     # so wait for the compile here — a one-time cost, like any JIT warm-up — and run one more untimed frame.
-    will_specialize = os.environ.get("PTB_SPECIALIZE", "") != "0" and len(scene_words(flat)) <= int(os.environ.get("PTB_SPEC_MAX_WORDS", "96"))
-    if will_specialize and args.warmup > 0:
+    if os.environ.get("PTB_SPECIALIZE", "") != "0" and args.warmup > 0:
         deadline = time.time() + 60
-        while not scene.specialized()[0] and time.time() < deadline:
+        waited = False
+        while not scene.specialized()[0] and scene.spec_pending and time.time() < deadline:
             time.sleep(0.05)
-        step(False)
+            waited = True
+        if waited:
+            step(False)
     sampler = ClockSampler(local_rank)
     barrier()
     sampler.start()
@@ -521,7 +533,7 @@ def run_ours(args):
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     hbm_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "6650 GB/s (of fallback)"
     passes = spec_total if spec_total else max(1, int(st.launches) // (2 + 2 * MAX_DEPTH))
-    kernels = kernel_rooflines(args.workload, flat.desc, st, n_pix, passes, fp32_peak, hbm_peak, spec_total > 0 and spec_passes == spec_total)
+    kernels = kernel_rooflines(args.workload, flat.desc, st, n_pix, passes, fp32_peak, hbm_peak, spec_total > 0 and spec_passes == spec_total, getattr(scene, "spec_camera_only", False))
     top = dict(max(kernels, key=lambda k: k["ms"]))
     fpr = trace_flops_per_ray(flat.desc)
     stage_ms = st.ms_primary + st.ms_bounce
@@ -554,7 +566,7 @@ def run_ours(args):
         steps4 = max(5, min(args.steps, 8))
         ms4, st4 = run_render(sc4, flat4, "c4", w4, h4, spp4, steps4, 2, args.samples_per_pass, torch, stream, acc4, out4)
         _, _, sp4, tot4 = sc4.specialized()
-        k4 = kernel_rooflines("c4", flat4.desc, st4, w4 * h4, tot4 if tot4 else max(1, int(st4.launches) // (2 + 2 * MAX_DEPTH)), fp32_peak, hbm_peak, tot4 > 0 and sp4 == tot4)
+        k4 = kernel_rooflines("c4", flat4.desc, st4, w4 * h4, tot4 if tot4 else max(1, int(st4.launches) // (2 + 2 * MAX_DEPTH)), fp32_peak, hbm_peak, tot4 > 0 and sp4 == tot4, getattr(sc4, "spec_camera_only", False))
         secondary["c4"] = {
             "config": workload_config("c4"), "metric": "Mrays/s", "value": st4.rays / (ms4 * 1e-3) / 1e6, "unit": "Mrays/s", "steps": steps4, "warmup": 2, "ms_per_step": ms4,
             "mpaths_per_s": st4.paths / (ms4 * 1e-3) / 1e6, "rays_per_path": st4.rays / max(1, st4.paths),

@@ -390,8 +390,10 @@ int ptb200_multi_shard(int spp, int nranks, int rank, int *count, int *offset, i
  * _probe needs no GPU: validates desc, writes the generated source (NUL-terminated, truncated to
  * source_capacity; *source_length = full length) and, when cubin_bytes != NULL, compiles it and reports
  * the size of the sm_100a cubin.
- * _specialized: 1 when the scene's specialised kernels are compiled and loaded, else 0; also reports how
- * many wavefront passes of the last render call that asked for stats ran them. */
+ * _specialized: 1 when the scene's specialised kernels are compiled and loaded (2: and, the program being
+ * large, the last render ran them for camera rays only and interpreted its queued rays), else 0 (with
+ * *compile_ms = -1 while a compile that a render call asked for is still under way); also reports
+ * how many wavefront passes of the last render call that asked for stats ran them. */
 int ptb200_specialize_probe(const PtbSceneDesc *desc, int which /* 0: render trace kernels, 1: ray-batch kernels, 2: the compiled program stream as hex text (tests) */, char *source, size_t source_capacity,
                             size_t *source_length, size_t *cubin_bytes);
 int ptb200_scene_specialized(PtbScene *scene, double *compile_ms, int *passes_specialized, int *passes_total);

@@ -1196,6 +1196,7 @@ struct SpecConfig
 {
     const SpecKernels *k = nullptr;
     CsgConfig cfg;
+    bool cameraOnly = false; // a large program: only the camera-ray kernel is worth specialising (see chooseSpec)
 };
 static int specMode()
 {
@@ -1224,7 +1225,13 @@ static int chooseSpec(PtbScene *s, uint32_t flags, double work, int which, SpecC
         const char *g = getenv("PTB_SPEC_GEN");
         return g && atoi(g) == 1 ? (size_t)96 : (size_t)PTB_SPEC_GEN2_MAX_WORDS;
     }();
-    if((flags & (PTB_FLAG_INTERPRET | PTB_FLAG_EXACT)) || (!force && (specMode() == 0 || s->fastHost.size() > maxWords)) || s->fastHost.size() > 4096)
+    // Larger programs (up to 4096 words) are specialised for CAMERA rays only, and only when the generated code
+    // tests bounding spheres before its shape-function calls (ptb_specialize.cu): a warp of camera rays — two pixels
+    // — then skips most of the scene (config 4: 87 % of the calls; 1 530 instructions a ray against the interpreter's
+    // 2 800, profiles/r02w_*).  Their queued rays stay interpreted: 32 unrelated rays skip nothing, and 130 KB of
+    // straight-line code lose to the interpreter's loop on instruction fetch.
+    const bool large = s->fastHost.size() > maxWords;
+    if((flags & (PTB_FLAG_INTERPRET | PTB_FLAG_EXACT)) || (!force && (specMode() == 0 || (large && which != SPEC_TRACE))) || s->fastHost.size() > 4096)
     {
         if(force)
             return fail(PTB_EINVAL, "PTB_FLAG_SPECIALIZE cannot be combined with PTB_FLAG_INTERPRET / PTB_FLAG_EXACT, and needs a program of at most 4096 words");
@@ -1232,6 +1239,16 @@ static int chooseSpec(PtbScene *s, uint32_t flags, double work, int which, SpecC
     }
     if(s->specSource[which].empty())
         s->specSource[which] = specializeSource(s->fastHost, s->fastTree, which);
+    if(large && !force)
+    {
+        static const bool largeOff = getenv("PTB_SPEC_LARGE") && atoi(getenv("PTB_SPEC_LARGE")) == 0;
+        if(largeOff || s->specSource[which].find("rlBoundMet(") == std::string::npos)
+        {
+            s->specNever[which] = true;
+            return PTB_OK;
+        }
+        sp.cameraOnly = true;
+    }
     const int mode = force || specMode() == 1 ? SPEC_WAIT : work >= 67108864.0 ? SPEC_START : SPEC_PEEK;
     std::string err;
     const SpecKernels *k = specializeGet(s->specSource[which], s->device, mode, err);
@@ -1411,13 +1428,13 @@ extern "C" int ptb200_scene_specialized(PtbScene *s, double *compile_ms, int *pa
     if(passes_total)
         *passes_total = s->lastPasses;
     const int which = s->specSource[SPEC_TRACE].empty() ? SPEC_INTERSECT : SPEC_TRACE; // a scene only used for ray batches has the ray-batch kernels
-    if(s->specSource[which].empty())
+    if(s->specSource[which].empty() || s->specNever[which])
         return 0;
     std::string err;
     const SpecKernels *k = specializeGet(s->specSource[which], s->device, SPEC_PEEK, err);
-    if(k && compile_ms)
-        *compile_ms = k->compileMs;
-    return k ? 1 : 0;
+    if(compile_ms)
+        *compile_ms = k ? k->compileMs : -1.0; // (-1: asked for, not there yet)
+    return k ? (s->lastSpecCameraOnly && which == SPEC_TRACE ? 2 : 1) : 0;
 }
 
 // ---- inspection entry points ------------------------------------------------------------------------
@@ -1684,6 +1701,7 @@ int ptb::renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbS
         if(sp.k)
         {
             specPasses++;
+            s->lastSpecCameraOnly = sp.cameraOnly;
             SPEC_LAUNCH(sp.k->tracePrimary, sp.cfg, stream, &devArg, &sp.cfg.cap, &sp.cfg.overflow, &sp.cfg.ovfStride, &pass, &hits);
         }
         else
@@ -1695,7 +1713,7 @@ int ptb::renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbS
             CU(cudaEventRecord(ev[2], stream));
         for(int b = 1; b <= pairLevels; b++)
         {
-            if(sp.k && specBounce)
+            if(sp.k && specBounce && !sp.cameraOnly)
             {
                 RayQueue qin = q[(b - 1) & 1];
                 const unsigned *cin = c + (b - 1);

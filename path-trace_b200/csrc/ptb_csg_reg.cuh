@@ -61,6 +61,13 @@ __device__ __forceinline__ uint4 ldsTab128(uint32_t a)
     return v;
 }
 #endif
+// A line through the origin along d against a bounding-sphere word {C, sqrt(|C|^2 - R^2)} (compileFastProgram,
+// ptb_capi.cu): it meets the sphere iff |C.d| >= |d| sqrt(|C|^2 - R^2).  sd = |d|.
+__device__ __forceinline__ bool rlBoundMet(const uint4 w, const V3 d, float sd)
+{
+    const float b = fmaf(__uint_as_float(w.x), d.x, fmaf(__uint_as_float(w.y), d.y, __uint_as_float(w.z) * d.z));
+    return fabsf(b) >= sd * __uint_as_float(w.w);
+}
 // Defined by the generated module: copies its table (if it has one) to shared memory at `tab`; all threads call it.
 __device__ __forceinline__ void specStageTable(uint32_t tab);
 

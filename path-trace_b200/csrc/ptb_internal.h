@@ -88,6 +88,8 @@ struct PtbScene
     std::vector<uint4> fastHost;
     ptb::FastTree fastTree;
     std::string specSource[2]; // SPEC_TRACE, SPEC_INTERSECT
+    bool specNever[2] = {false, false}; // a large program whose generated code has no bounding-sphere tests: stays interpreted
+    bool lastSpecCameraOnly = false; // the last render ran the specialised kernel for camera rays only (a large program)
     int lastSpecPasses = 0, lastPasses = 0; // of the last render call with stats
     int specSeen[2] = {0, 0};               // calls that wanted the specialised kernels of each kind so far
     ptb::DeviceBuffer specOverflow;

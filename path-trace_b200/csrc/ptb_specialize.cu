@@ -392,6 +392,72 @@ struct Gen
         s.swap(keep);
         return f;
     }
+    // ---- bounding spheres (camera rays) ------------------------------------------------------------------------------
+    // {C, sqrt(|C|^2 - R^2)} per sphere leaf: what compileFastProgram stores behind FK_END for the leaves of sphere
+    // runs (ptb_capi.cu), computed here for untransformed spheres.  boundsOf() lists the spheres a subtree's result
+    // lies within — {} when EVERY line that misses all of them leaves the subtree empty: a Union needs both operands
+    // bounded, a Difference its left one, an Intersection either.
+    std::map<size_t, uint4> runBound; // header word of a transformed-sphere leaf -> its bounding-sphere word
+    int divergent = 0;                // > 0: the code being emitted runs under a per-lane condition
+    bool usesBounds = false;
+    void indexRunBounds()
+    {
+        for(const FastTreeItem &it : tree.items)
+        {
+            if(it.kind != PTB_OP_PUSH_PRIM || it.leafWord < 0)
+                continue;
+            const size_t w = (size_t)it.leafWord;
+            const uint32_t x = prog[w].x, table = (x >> 16) & 0x3FFFu;
+            if((x & FK_SPHERE_XF) && (x & (FH_RUN | FH_TAIL)) == FH_RUN && table != 0u)
+                for(uint32_t k = 0; k < ((x >> 12) & 15u); k++)
+                    runBound[w + 4u * k] = prog[table + k];
+        }
+    }
+    bool boundsOf(int id, std::vector<uint4> &out) const
+    {
+        const GenNode &n = nodes[id];
+        if(n.left < 0)
+        {
+            const size_t w = (size_t)tree.items[n.item].leafWord;
+            const uint4 h = prog[w];
+            if(h.x & FK_SPHERE_XF)
+            {
+                auto it = runBound.find(w);
+                if(it == runBound.end())
+                    return false;
+                out.push_back(it->second);
+                return true;
+            }
+            if(h.x & FK_SPHERE)
+            { // header {x, tags, -r^2, c0}, then (-c.xyz, 0)
+                auto f = [](uint32_t u) {
+                    float v;
+                    memcpy(&v, &u, 4);
+                    return (double)v;
+                };
+                const double cx = -f(prog[w + 1].x), cy = -f(prog[w + 1].y), cz = -f(prog[w + 1].z), r2 = -f(h.z) * 1.002 + 1e-9;
+                const double K = cx * cx + cy * cy + cz * cz - r2;
+                const float c[4] = {(float)cx, (float)cy, (float)cz, (float)(K > 0 ? sqrt(K) * (1.0 - 1e-5) : 0.0)};
+                uint4 word;
+                memcpy(&word, c, 16);
+                out.push_back(word);
+                return true;
+            }
+            return false; // a plane
+        }
+        const int kind = tree.items[n.item].kind;
+        if(kind == PTB_OP_UNION)
+            return boundsOf(n.left, out) && boundsOf(n.right, out);
+        const size_t mark = out.size();
+        if(boundsOf(n.left, out))
+            return true;
+        out.resize(mark);
+        if(kind == PTB_OP_INTERSECTION && boundsOf(n.right, out))
+            return true;
+        out.resize(mark);
+        return false;
+    }
+
     // A subtree of a chosen shape: its constants go to the table, its code is a call.  The callee starts with an
     // empty stack of its own on top of ours, so a result of two or more spans lies at our `top` (ptb_csg_reg.cuh).
     void emitCall(int id, int indent)
@@ -403,7 +469,30 @@ struct Gen
         for(size_t w : words)
             table.push_back(prog[w]);
         const std::string L = "L" + std::to_string(id);
-        line(indent, "RList " + L + ";");
+        // Camera rays: if no ray of the warp meets any of the spheres the subtree's result lies within, the result
+        // is empty for all of them and the call is not made (two pixels a warp: 87 % of the calls of config 4).
+        std::vector<uint4> bounds;
+        const bool bounded = divergent == 0 && !inFn && getenv("PTB_SPEC_BOUNDS") == nullptr ? boundsOf(id, bounds) && !bounds.empty() && bounds.size() <= 32 : false;
+        const size_t bbase = table.size();
+        if(bounded)
+        {
+            usesBounds = true;
+            for(const uint4 &b : bounds)
+                table.push_back(b);
+        }
+        line(indent, "RList " + L + " = rlEmpty();");
+        if(bounded)
+        {
+            line(indent, "bool skip" + std::to_string(id) + " = false;");
+            line(indent, "if(O0)");
+            line(indent, "{");
+            line(indent + 1, "uint32_t met_ = 0u;");
+            line(indent + 1, "for(uint32_t k_ = 0u; k_ < " + std::to_string(bounds.size()) + "u; k_++)");
+            line(indent + 2, "met_ |= rlBoundMet(ldsTab128(ev.tab + " + std::to_string(16 * bbase) + "u + 16u * k_), d, sd_) ? 1u : 0u;");
+            line(indent + 1, "skip" + std::to_string(id) + " = __reduce_or_sync(0xFFFFFFFFu, met_) == 0u;");
+            line(indent, "}");
+            line(indent, "if(!skip" + std::to_string(id) + ")");
+        }
         line(indent, "{");
         line(indent + 1, "const uint4 r_ = ptbShape" + std::to_string(f) + "<O0>(ev.poolBase, ev.cap, ev.top, o.x, o.y, o.z, d.x, d.y, d.z, ev.tab + " + std::to_string(16 * base) + "u);");
         line(indent + 1, L + ".n = (int)(r_.x & 0x7FFFFFFFu), " + L + ".a = rlSpan(__uint_as_float(r_.y), __uint_as_float(r_.z), r_.w), " + L + ".base = ev.top;");
@@ -522,7 +611,9 @@ struct Gen
             line(indent + 1, "}");
             line(indent + 1, "else");
             line(indent + 1, "{");
+            divergent++;
             node(id, indent + 2, false, true); // declares L<id>_sub
+            divergent--;
             line(indent + 2, "L" + std::to_string(id) + " = L" + std::to_string(id) + "_sub;");
             line(indent + 1, "}");
             line(indent, "}");
@@ -538,7 +629,9 @@ struct Gen
             line(indent, "RList " + rname + " = rlEmpty();");
             line(indent, "if(" + var(n.left) + ".n != 0)");
             line(indent, "{");
+            divergent++;
             node(n.right, indent + 1);
+            divergent--;
             line(indent + 1, rname + " = " + var(n.right) + ";");
             line(indent, "}");
         }
@@ -584,6 +677,7 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
             nLeaves += it.kind == PTB_OP_PUSH_PRIM;
         if(mode != 0 && (mode == 1 || nLeaves >= 24))
         {
+            g.indexRunBounds();
             g.computeShapes();
             g.chooseShapes(root, mode == 1 ? 3 : 4);
         }
@@ -598,6 +692,7 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
     if(which == SPEC_TRACE)
     { // the renderer's trace kernels only want the first boundary with t >= eps
         g.s += "template <bool O0>\n__device__ __forceinline__ int specTrace(REval &ev, const V3 o, const V3 d, float &t, uint32_t &tag)\n{\n";
+        g.line(1, "const float sd_ = O0 ? Ar<false>::sqrt(fmaf(d.x, d.x, fmaf(d.y, d.y, d.z * d.z))) : 0.f; // |d| for the bounding-sphere tests (unused: dropped)");
         if(fusedRoot)
         { // the root Union is scanned while it is merged; its right operand (a leaf or a plane cluster) stays in registers
             g.node(rn.left, 1);
@@ -623,6 +718,7 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
     else
     { // ray batches want the whole root list: pool slots [0, n)
         g.s += "template <bool O0>\n__device__ __forceinline__ int specList(REval &ev, const V3 o, const V3 d)\n{\n";
+        g.line(1, "const float sd_ = O0 ? Ar<false>::sqrt(fmaf(d.x, d.x, fmaf(d.y, d.y, d.z * d.z))) : 0.f;");
         g.node(root, 1);
         g.line(1, "return rlToPool(ev, " + g.var(root) + ");");
         g.s += "}\n";

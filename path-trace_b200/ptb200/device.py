@@ -129,12 +129,16 @@ class DeviceScene:
         return out, source, lattice, stats, astats
 
     def specialized(self):
-        """ptb200_scene_specialized: (kernels ready?, compile ms, passes of the last stats render that ran them, passes)."""
+        """ptb200_scene_specialized: (kernels ready?, compile ms, passes of the last stats render that ran them, passes);
+        self.spec_camera_only: the last render ran them for camera rays only (a large program); self.spec_pending: a
+        compile a render call asked for is still under way."""
         ms, a, b = C.c_double(), C.c_int(), C.c_int()
         rc = capi.product().ptb200_scene_specialized(self.handle, C.byref(ms), C.byref(a), C.byref(b))
         if rc < 0:
             check(rc)
-        return rc == 1, ms.value, a.value, b.value
+        self.spec_camera_only = rc == 2
+        self.spec_pending = rc == 0 and ms.value < 0
+        return rc >= 1, ms.value, a.value, b.value
 
     def render_accumulate(self, params, accum, stream=None, want_stats=True):
         """Adds this call's radiance sums into a device (H, W, 4) float32 torch tensor."""
