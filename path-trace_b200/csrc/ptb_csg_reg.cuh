@@ -361,6 +361,61 @@ __device__ __forceinline__ void rlIntersectionInto(REval &ev, RList &A, const RL
         A = rlGeneral(ev, DK_INTERSECTION, A, B);
 }
 
+// The same three with everything but the empty-operand tests in ONE out-of-line function, for large programs: inlined
+// at every operator the closed forms and the call of the general merge are ~120 instructions each, most of them never
+// executed by a warp of camera rays, and the straight-line code of a 70-leaf scene stops fitting the instruction
+// cache (ncu, config 4: 5.4 stall cycles per issue waiting for instructions, profiles/r02w_spec_c4.txt).
+struct RMerged
+{
+    RList L;
+    int top;
+    bool ovf;
+};
+static __device__ __noinline__ RMerged rlMergeSlow(int kind, uint32_t poolBase, int cap, int top, RList A, RList B)
+{
+    REval ev;
+    ev.poolBase = poolBase, ev.cap = cap, ev.top = top, ev.ovf = false, ev.tab = 0u;
+    RMerged r;
+    if(A.n == 1 && B.n == 1)
+        r.L = kind == DK_UNION ? rlUnion11(ev, A.a, B.a) : kind == DK_DIFFERENCE ? rlDifference11(ev, A.a, B.a) : rlIntersection11(A.a, B.a);
+    else
+        r.L = rlGeneral(ev, kind, A, B);
+    r.top = ev.top, r.ovf = ev.ovf;
+    return r;
+}
+__device__ __forceinline__ void rlMergeCold(REval &ev, int kind, RList &A, const RList &B)
+{
+    const RMerged r = rlMergeSlow(kind, ev.poolBase, ev.cap, ev.top, A, B);
+    A = r.L, ev.top = r.top, ev.ovf = ev.ovf || r.ovf;
+}
+__device__ __forceinline__ void rlUnionIntoCold(REval &ev, RList &A, const RList &B)
+{
+    if(B.n == 0)
+        return;
+    if(A.n == 0)
+        A = B;
+    else
+        rlMergeCold(ev, DK_UNION, A, B);
+}
+__device__ __forceinline__ void rlDifferenceIntoCold(REval &ev, RList &A, const RList &B)
+{
+    if(B.n == 0 || A.n == 0)
+        return;
+    rlMergeCold(ev, DK_DIFFERENCE, A, B);
+}
+__device__ __forceinline__ void rlIntersectionIntoCold(REval &ev, RList &A, const RList &B)
+{
+    if(A.n == 0)
+        return;
+    if(B.n == 0)
+    {
+        rlRelease(ev, A, B);
+        A.n = 0;
+    }
+    else
+        rlMergeCold(ev, DK_INTERSECTION, A, B);
+}
+
 // ---- the root -----------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ SpanRec rlGet(const REval &ev, const RList &L, int i)
 {

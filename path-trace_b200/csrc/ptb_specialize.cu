@@ -399,6 +399,7 @@ struct Gen
     // bounded, a Difference its left one, an Intersection either.
     std::map<size_t, uint4> runBound; // header word of a transformed-sphere leaf -> its bounding-sphere word
     int divergent = 0;                // > 0: the code being emitted runs under a per-lane condition
+    bool coldMerges = false;          // large programs: operators call ONE out-of-line merge (rlMergeSlow, ptb_csg_reg.cuh)
     bool usesBounds = false;
     void indexRunBounds()
     {
@@ -637,7 +638,7 @@ struct Gen
         }
         const std::string rhs = kind == PTB_OP_UNION ? var(n.right) : "L" + std::to_string(n.right) + "_r";
         const char *fn = kind == PTB_OP_UNION ? "rlUnionInto" : kind == PTB_OP_DIFFERENCE ? "rlDifferenceInto" : "rlIntersectionInto";
-        line(indent, std::string(fn) + "(ev, " + var(n.left) + ", " + rhs + ");");
+        line(indent, std::string(fn) + (coldMerges ? "Cold" : "") + "(ev, " + var(n.left) + ", " + rhs + ");");
         if(asCluster)
             alias[id] = n.left; // from here on this node's list IS the left operand's variable
         else
@@ -678,6 +679,7 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
         if(mode != 0 && (mode == 1 || nLeaves >= 24))
         {
             g.indexRunBounds();
+            g.coldMerges = !getenv("PTB_SPEC_COLD") || atoi(getenv("PTB_SPEC_COLD")) != 0;
             g.computeShapes();
             g.chooseShapes(root, mode == 1 ? 3 : 4);
         }
