@@ -384,7 +384,9 @@ int ptb200_multi_shard(int spp, int nranks, int rank, int *count, int *offset, i
  * By default a render / ray batch with >= 2^26 rays to trace starts that compile on a background thread
  * and switches over when it is done (between passes, if need be); compiled kernels are kept per process
  * and per distinct scene program (at most 64 programs per process, one background compile at a time: further
- * scenes stay interpreted).  Environment: PTB_SPECIALIZE=0 never, =1 compile and wait at first
+ * scenes stay interpreted).  Programs of more than 96 words are specialised for camera rays only, and only when
+ * the generated code can test bounding spheres before its calls (csrc/ptb_specialize.cu); PTB_SPEC_LARGE=0 keeps
+ * them interpreted.  Environment: PTB_SPECIALIZE=0 never, =1 compile and wait at first
  * use.  Flags: PTB_FLAG_SPECIALIZE / PTB_FLAG_INTERPRET per call.  No reference counterpart (the
  * reference walks a tree of virtual SpanIterators, include/object.h:10-24).
  * _probe needs no GPU: validates desc, writes the generated source (NUL-terminated, truncated to
