@@ -172,10 +172,28 @@ RenderScratch::~RenderScratch()
         cudaEventDestroy(e);
 }
 
+// Is this host buffer page-locked (cudaHostAlloc / cudaHostRegister / torch pin_memory)?  Then it is DMA-ed from
+// where it lies; a pageable one goes through the pinned staging halves (a CPU copy at ~10 GB/s).
+bool hostIsPinned(const void *p)
+{
+    cudaPointerAttributes attr;
+    if(cudaPointerGetAttributes(&attr, p) != cudaSuccess)
+    {
+        cudaGetLastError();
+        return false;
+    }
+    return attr.type == cudaMemoryTypeHost;
+}
 // Host -> linear device memory from a pageable buffer, through the pinned staging halves: the CPU copy of
 // piece k+1 overlaps the DMA of piece k (the driver's own pageable path ran at < 2 GB/s here).
 int uploadLinear(void *dst, const void *src, size_t bytes)
 {
+    if(hostIsPinned(src))
+    {
+        CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, nullptr));
+        CU(cudaStreamSynchronize(nullptr));
+        return PTB_OK;
+    }
     std::lock_guard<std::mutex> g(g_stagingLock);
     if(int rc = stagingInit())
         return rc;
@@ -221,19 +239,28 @@ void PtbScene::quiesce()
 
 namespace
 {
-template <typename T>
-int upload(PtbScene *s, const std::vector<T> &host, const T **out)
+// The scene's tables are laid out in ONE host image and go to the device with one copy into one block from the
+// library's cache: ten cudaMalloc + cudaMemcpy pairs per ptb200_scene_create (and ten cudaFree per destroy) cost
+// 5-240 ms a scene, erratically, in a process that holds tens of GB of queues.
+struct TableImage
 {
-    *out = nullptr;
-    size_t bytes = std::max<size_t>(host.size(), 1) * sizeof(T);
-    void *p = nullptr;
-    CU(cudaMalloc(&p, bytes));
-    s->allocs.push_back(p);
-    if(!host.empty())
-        CU(cudaMemcpy(p, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice));
-    *out = (const T *)p;
-    return PTB_OK;
-}
+    std::vector<char> host;
+    template <typename T>
+    size_t add(const std::vector<T> &v)
+    {
+        const size_t at = (host.size() + 255) & ~(size_t)255;
+        host.resize(at + std::max<size_t>(v.size(), 1) * sizeof(T), 0);
+        if(!v.empty())
+            memcpy(host.data() + at, v.data(), v.size() * sizeof(T));
+        return at;
+    }
+    size_t reserve(size_t bytes)
+    {
+        const size_t at = (host.size() + 255) & ~(size_t)255;
+        host.resize(at + bytes, 0);
+        return at;
+    }
+};
 
 // deviceLinear != NULL: the pixels are already on this device as a linear RGBA32F buffer (multi-GPU create)
 int createImage(const float *rgba, int w, int h, ImageSlot &slot, const float4 *deviceLinear = nullptr)
@@ -260,7 +287,7 @@ int createImage(const float *rgba, int w, int h, ImageSlot &slot, const float4 *
     const size_t rowBytes = (size_t)w * 16;
     if(deviceLinear)
         CU(cudaMemcpy2DToArray(slot.array, 0, 0, deviceLinear, rowBytes, rowBytes, (size_t)h, cudaMemcpyDeviceToDevice));
-    else if((size_t)h * rowBytes < (size_t(1) << 20) || rowBytes > kStagingHalf)
+    else if((size_t)h * rowBytes < (size_t(1) << 20) || rowBytes > kStagingHalf || hostIsPinned(rgba))
         CU(cudaMemcpy2DToArray(slot.array, 0, 0, rgba, rowBytes, rowBytes, (size_t)h, cudaMemcpyHostToDevice));
     else
     { // the caller's buffer is pageable: copy it through pinned staging in 8 MB pieces, the CPU copy of
@@ -1034,10 +1061,19 @@ int ptb::sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> 
     DevScene &dev = s->dev;
     memset(&dev, 0, sizeof(dev));
     int rc;
-    if((rc = upload(s, prog, &dev.program)) || (rc = upload(s, fast, &dev.fastProgram)) || (rc = upload(s, geo, &dev.primGeo)) || (rc = upload(s, meta, &dev.primMeta)) ||
-       (rc = upload(s, chainXf, &dev.chainXf)) || (rc = upload(s, xf, &dev.xforms)) || (rc = upload(s, mats, &dev.materials)) ||
-       (rc = upload(s, texops, &dev.texops)) || (rc = upload(s, texdata, &dev.texdata)) || (rc = upload(s, baked, &dev.texBaked)))
-        return rc;
+    TableImage img;
+    const size_t oProg = img.add(prog), oFast = img.add(fast), oGeo = img.add(geo), oMeta = img.add(meta), oChain = img.add(chainXf), oXf = img.add(xf), oMats = img.add(mats),
+                 oTexops = img.add(texops), oTexdata = img.add(texdata), oBaked = img.add(baked);
+    const int imageSlots = std::max(16, 2 * d->n_images);
+    const size_t oImages = img.reserve((size_t)imageSlots * sizeof(DevImage));
+    CU(s->tables.ensure(std::max<size_t>(img.host.size(), size_t(1) << 20))); // (>= 1 MiB: blocks that size go back to the cache)
+    char *base = (char *)s->tables.p;
+    CU(cudaMemcpy(base, img.host.data(), img.host.size(), cudaMemcpyHostToDevice));
+    dev.program = (const uint4 *)(base + oProg), dev.fastProgram = (const uint4 *)(base + oFast), dev.primGeo = (const float4 *)(base + oGeo);
+    dev.primMeta = (const int4 *)(base + oMeta), dev.chainXf = (const int *)(base + oChain), dev.xforms = (const float4 *)(base + oXf);
+    dev.materials = (const DevMaterial *)(base + oMats), dev.texops = (const int2 *)(base + oTexops), dev.texdata = (const float *)(base + oTexdata);
+    dev.texBaked = (const DevTexBaked *)(base + oBaked);
+    s->dImages = (DevImage *)(base + oImages), s->imageCapacity = imageSlots;
     dev.programWords = (int)prog.size();
     dev.fastWords = (int)fast.size();
     dev.nPrims = d->n_prims, dev.nMaterials = d->n_materials, dev.nTexops = d->n_texops;

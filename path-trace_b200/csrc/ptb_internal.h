@@ -77,6 +77,7 @@ struct PtbScene
     std::vector<ptb::ImageSlot> images;
     ptb::DevImage *dImages = nullptr;
     int imageCapacity = 0;
+    ptb::DeviceBuffer tables; // every scene table (programs, primitives, transforms, materials, textures, image table) in ONE block, taken from and returned to the library's block cache
     std::mutex lock; // one render / intersect call at a time per scene
     ptb::RenderScratch scratch;
     bool asyncBusy = false;
@@ -137,6 +138,7 @@ int checkParams(const PtbRenderParams *p, int &x0, int &y0, int &rw, int &rh);
 // The wavefront driver.  Caller holds scene->lock and has made scene->device current.
 int renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbStats *stats, cudaStream_t stream, const PixelListArg *points = nullptr);
 // Host -> linear device memory through the pinned staging halves (pageable source), on the default stream; synchronous.
+bool hostIsPinned(const void *p);
 int uploadLinear(void *dst, const void *src, size_t bytes);
 
 } // namespace ptb

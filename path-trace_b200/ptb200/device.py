@@ -23,6 +23,22 @@ class Flat:
         self.desc = PtbSceneDesc()
         lib.ptbh_flatten_desc(self.handle, C.byref(self.desc))
 
+    def pin_images(self):
+        """Moves the image pixels into page-locked host memory (torch) and points the description at the copies:
+        ptb200_scene_create then DMAs them from where they lie instead of staging them through its own pinned
+        buffer.  What a caller that re-creates scenes every frame would do."""
+        import torch
+
+        self._pinned = []
+        for i in range(self.desc.n_images):
+            im = self.desc.images[i]
+            n = 4 * im.width * im.height
+            t = torch.empty(n, dtype=torch.float32, pin_memory=True)
+            C.memmove(t.data_ptr(), im.rgba, 4 * n)
+            self._pinned.append(t)
+            self.desc.images[i].rgba = C.cast(t.data_ptr(), type(im.rgba))
+        return self
+
     def close(self):
         if self.handle:
             capi.product().ptbh_flatten_free(self.handle)
