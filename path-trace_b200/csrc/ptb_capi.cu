@@ -1003,7 +1003,8 @@ int ptb::sceneCreateImpl(const PtbSceneDesc *d, PtbScene *s, std::vector<uint4> 
     // Fold the chains the materials start (DevTexBaked, ptb_scene_dev.cuh); validateTexture has bounded every chain.
     std::vector<DevTexBaked> baked((size_t)std::max(1, d->n_texops));
     memset(baked.data(), 0, baked.size() * sizeof(DevTexBaked));
-    for(int i = 0; i < d->n_materials; i++)
+    const bool foldTextures = !getenv("PTB_TEX_FOLD") || atoi(getenv("PTB_TEX_FOLD")) != 0; // (tests: 0 = every chain through the interpreter)
+    for(int i = 0; foldTextures && i < d->n_materials; i++)
         for(int k = 0; k < 5; k++)
         {
             const int root = d->materials[i].tex[k];

@@ -25,9 +25,13 @@ MEAN_TOL = 0.005      # |mean(gpu) - mean(ref)| / mean(ref)
 RMSE_TOL = {"c1": 0.03, "c2": 0.01, "c4": 0.012, "c5": 0.05}  # measured on B200: 0.016, 0.0053, 0.0054, 0.025  # per-pixel RMS error / mean(ref); sample counts per case: golden_cases.RENDER_SETUP
 
 
-def test_texture_known_answers():
+@pytest.mark.parametrize("fold", ["1", "0"])
+def test_texture_known_answers(fold, monkeypatch):
     """Point-sampled texture programs: same texel as the reference except where float rounding of
-    atan2/asin/log moves a lookup across a texel edge (<= 1% of positions), values within 1e-5."""
+    atan2/asin/log moves a lookup across a texel edge (<= 1% of positions), values within 1e-5.
+    Through the records chains are folded into at scene create (DevTexBaked: every chain here but `const`,
+    `moved_const` and `double_affine`) and, with PTB_TEX_FOLD=0, through the interpreter."""
+    monkeypatch.setenv("PTB_TEX_FOLD", fold)
     b = product_builder()
     pos = gc.kat_positions()
     for name, tex in gc.kat_textures(b).items():
@@ -278,3 +282,38 @@ def test_cpp_host_render_and_span_iterator():
     assert lib.ptbh_render(w2, C.byref(p), out.ctypes.data, None) == 0
     direct, _ = device.DeviceScene(device.Flat(w2)).render(device.default_params(96, 54, 256, seed=2))
     assert np.allclose(out, direct, rtol=1e-4, atol=1e-5)
+
+
+def test_page_locked_image_buffers_give_the_same_scene():
+    """ptb200_scene_create DMAs image pixels straight from page-locked memory (device.Flat.pin_images) and stages
+    pageable ones through its own pinned buffer: the same scene either way."""
+    pytest.importorskip("torch")
+    b = product_builder()
+    flat = device.Flat(gc.render_scene(b, "c5", small=True))
+    p = device.default_params(96, 54, 16, seed=11)
+    a, _ = device.DeviceScene(flat).render(p)
+    flat.pin_images()
+    c, _ = device.DeviceScene(flat).render(p)
+    assert np.allclose(a, c, rtol=1e-5, atol=1e-6)  # (float atomics: the order of a pixel's sums is not fixed)
+
+
+def test_large_programs_specialise_the_camera_ray_kernel_only():
+    """Config 4 (70 leaves, 340 program words) is beyond the size that is specialised whole; its camera rays run a
+    generated kernel whose shape-function calls are guarded by bounding-sphere votes, its queued rays the interpreter
+    (ptb200_scene_specialized == 2), and the image is the interpreter's up to the order of the float atomics."""
+    if os.environ.get("PTB_SPECIALIZE", "") == "0" or os.environ.get("PTB_SPEC_LARGE", "") == "0":
+        pytest.skip("specialisation switched off by the environment")
+    b = product_builder()
+    flat = device.Flat(gc.render_scene(b, "c4", small=True))
+    sc = device.DeviceScene(flat)
+    sc.render(device.default_params(1920, 1080, 33, seed=1))  # >= 2^26 rays: starts the compile on a background thread
+    deadline = time.time() + 180
+    while not sc.specialized()[0] and time.time() < deadline:
+        assert sc.spec_pending, "the library decided not to specialise config 4"
+        time.sleep(0.1)
+    assert sc.specialized()[0], "NVRTC compile of the camera-ray kernel did not finish in 180 s"
+    a, _ = sc.render(device.default_params(160, 90, 32, seed=21))
+    ready, ms, passes, total = sc.specialized()
+    assert ready and sc.spec_camera_only and passes == total > 0 and ms > 0
+    i, _ = device.DeviceScene(flat).render(device.default_params(160, 90, 32, seed=21, flags=capi.PTB_FLAG_INTERPRET))
+    assert np.allclose(a, i, rtol=1e-4, atol=1e-5)
