@@ -1279,7 +1279,7 @@ static int chooseSpec(PtbScene *s, uint32_t flags, double work, int which, SpecC
     if(large && !force)
     {
         static const bool largeOff = getenv("PTB_SPEC_LARGE") && atoi(getenv("PTB_SPEC_LARGE")) == 0;
-        if(largeOff || s->specSource[which].find("rlBoundMet(") == std::string::npos)
+        if(largeOff || s->specSource[which].find("PTB_SPEC_BOUNDED_CALLS") == std::string::npos)
         {
             s->specNever[which] = true;
             return PTB_OK;

@@ -388,32 +388,41 @@ __device__ __forceinline__ void rlMergeCold(REval &ev, int kind, RList &A, const
     const RMerged r = rlMergeSlow(kind, ev.poolBase, ev.cap, ev.top, A, B);
     A = r.L, ev.top = r.top, ev.ovf = ev.ovf || r.ovf;
 }
+// (PTB_UNLIKELY: the merge proper goes to the end of the function, out of the way of the code every ray runs)
+#ifdef PTB_HOST_EMU
+#define PTB_UNLIKELY(x) (x)
+#define PTB_LIKELY(x) (x)
+#else
+#define PTB_UNLIKELY(x) __builtin_expect(!!(x), 0)
+#define PTB_LIKELY(x) __builtin_expect(!!(x), 1)
+#endif
 __device__ __forceinline__ void rlUnionIntoCold(REval &ev, RList &A, const RList &B)
 {
-    if(B.n == 0)
-        return;
-    if(A.n == 0)
-        A = B;
-    else
-        rlMergeCold(ev, DK_UNION, A, B);
+    if(PTB_UNLIKELY(B.n != 0))
+    {
+        if(A.n == 0)
+            A = B;
+        else
+            rlMergeCold(ev, DK_UNION, A, B);
+    }
 }
 __device__ __forceinline__ void rlDifferenceIntoCold(REval &ev, RList &A, const RList &B)
 {
-    if(B.n == 0 || A.n == 0)
-        return;
-    rlMergeCold(ev, DK_DIFFERENCE, A, B);
+    if(PTB_UNLIKELY(B.n != 0 && A.n != 0))
+        rlMergeCold(ev, DK_DIFFERENCE, A, B);
 }
 __device__ __forceinline__ void rlIntersectionIntoCold(REval &ev, RList &A, const RList &B)
 {
-    if(A.n == 0)
-        return;
-    if(B.n == 0)
+    if(PTB_UNLIKELY(A.n != 0))
     {
-        rlRelease(ev, A, B);
-        A.n = 0;
+        if(B.n == 0)
+        {
+            rlRelease(ev, A, B);
+            A.n = 0;
+        }
+        else
+            rlMergeCold(ev, DK_INTERSECTION, A, B);
     }
-    else
-        rlMergeCold(ev, DK_INTERSECTION, A, B);
 }
 
 // ---- the root -----------------------------------------------------------------------------------------------------------

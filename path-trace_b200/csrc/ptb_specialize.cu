@@ -278,6 +278,7 @@ struct Gen
     std::map<std::string, int> shapeProto; // chosen signature -> the node whose code becomes the function's body
     std::vector<std::string> fnDefs;
     std::vector<bool> fnDone;
+    std::vector<size_t> fnBounds; // bounding-sphere words an instance of each function brings (0: the function has no test)
     std::vector<uint4> table; // all instances' constants
     bool inFn = false;
 
@@ -360,6 +361,7 @@ struct Gen
             }
         }
         fnDone.assign(shapeFn.size(), false);
+        fnBounds.assign(shapeFn.size(), 0);
         fnDefs.assign(shapeFn.size(), std::string());
     }
     int ensureFn(const std::string &sg)
@@ -378,7 +380,30 @@ struct Gen
         tableMode = inFn = true;
         s += "// shape " + sg + "\n";
         s += "template <bool O0>\nstatic __device__ __noinline__ uint4 ptbShape" + std::to_string(f) +
-             "(uint32_t poolBase, int cap, int top, float ox, float oy, float oz, float dx, float dy, float dz, uint32_t tb)\n{\n";
+             "(uint32_t poolBase, int cap, int top, float ox, float oy, float oz, float dx, float dy, float dz, uint32_t tb, uint32_t bt)\n{\n";
+        { // Camera rays, bt != 0 (a call site all lanes reach together): the bounding spheres the instance's result lies
+          // within, boundsN words at shared address bt.  No ray of the warp meets any of them: the result is empty.  The
+          // test sits HERE, not at the call sites, so that the code every warp runs eight times over is these few dozen
+          // instructions and stays in the instruction cache.
+            std::vector<uint4> protoBounds;
+            const size_t nb = boundsOf(proto, protoBounds) ? protoBounds.size() : 0;
+            fnBounds[f] = nb;
+            if(nb > 0 && nb <= 32)
+            {
+                line(1, "if(O0 && bt != 0u)");
+                line(1, "{");
+                line(2, "const V3 dv = mk(dx, dy, dz);");
+                line(2, "const float sd = Ar<false>::sqrt(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));");
+                line(2, "uint32_t met = 0u;");
+                line(2, "for(uint32_t k = 0u; k < " + std::to_string(nb) + "u; k++)");
+                line(3, "met |= rlBoundMet(ldsTab128(bt + 16u * k), dv, sd) ? 1u : 0u;");
+                line(2, "if(__reduce_or_sync(0xFFFFFFFFu, met) == 0u)");
+                line(3, "return make_uint4(0u, 0u, 0u, 0u);");
+                line(1, "}");
+            }
+            else
+                fnBounds[f] = 0;
+        }
         line(1, "REval ev;");
         line(1, "ev.poolBase = poolBase, ev.cap = cap, ev.top = top, ev.ovf = false, ev.tab = 0u;");
         line(1, "const V3 o = mk(ox, oy, oz), d = mk(dx, dy, dz);");
@@ -470,10 +495,10 @@ struct Gen
         for(size_t w : words)
             table.push_back(prog[w]);
         const std::string L = "L" + std::to_string(id);
-        // Camera rays: if no ray of the warp meets any of the spheres the subtree's result lies within, the result
-        // is empty for all of them and the call is not made (two pixels a warp: 87 % of the calls of config 4).
+        // Camera rays: the callee first votes on the bounding spheres the instance's result lies within (see ensureFn);
+        // their words follow the instance's constants in the table.  Only where all lanes arrive together.
         std::vector<uint4> bounds;
-        const bool bounded = divergent == 0 && !inFn && getenv("PTB_SPEC_BOUNDS") == nullptr ? boundsOf(id, bounds) && !bounds.empty() && bounds.size() <= 32 : false;
+        const bool bounded = divergent == 0 && !inFn && getenv("PTB_SPEC_BOUNDS") == nullptr && fnBounds[f] > 0 && boundsOf(id, bounds) && bounds.size() == fnBounds[f];
         const size_t bbase = table.size();
         if(bounded)
         {
@@ -481,21 +506,10 @@ struct Gen
             for(const uint4 &b : bounds)
                 table.push_back(b);
         }
-        line(indent, "RList " + L + " = rlEmpty();");
-        if(bounded)
-        {
-            line(indent, "bool skip" + std::to_string(id) + " = false;");
-            line(indent, "if(O0)");
-            line(indent, "{");
-            line(indent + 1, "uint32_t met_ = 0u;");
-            line(indent + 1, "for(uint32_t k_ = 0u; k_ < " + std::to_string(bounds.size()) + "u; k_++)");
-            line(indent + 2, "met_ |= rlBoundMet(ldsTab128(ev.tab + " + std::to_string(16 * bbase) + "u + 16u * k_), d, sd_) ? 1u : 0u;");
-            line(indent + 1, "skip" + std::to_string(id) + " = __reduce_or_sync(0xFFFFFFFFu, met_) == 0u;");
-            line(indent, "}");
-            line(indent, "if(!skip" + std::to_string(id) + ")");
-        }
+        line(indent, "RList " + L + ";");
         line(indent, "{");
-        line(indent + 1, "const uint4 r_ = ptbShape" + std::to_string(f) + "<O0>(ev.poolBase, ev.cap, ev.top, o.x, o.y, o.z, d.x, d.y, d.z, ev.tab + " + std::to_string(16 * base) + "u);");
+        line(indent + 1, "const uint4 r_ = ptbShape" + std::to_string(f) + "<O0>(ev.poolBase, ev.cap, ev.top, o.x, o.y, o.z, d.x, d.y, d.z, ev.tab + " + std::to_string(16 * base) + "u, " +
+                             (bounded ? "ev.tab + " + std::to_string(16 * bbase) + "u" : "0u") + ");");
         line(indent + 1, L + ".n = (int)(r_.x & 0x7FFFFFFFu), " + L + ".a = rlSpan(__uint_as_float(r_.y), __uint_as_float(r_.z), r_.w), " + L + ".base = ev.top;");
         line(indent + 1, "ev.ovf = ev.ovf || (r_.x >> 31) != 0u;");
         line(indent + 1, "if(" + L + ".n >= 2)");
@@ -605,7 +619,7 @@ struct Gen
             line(indent, "RList " + var(id) + ";");
             line(indent, "{");
             planeFoldCalls(indent + 1, w, extra);
-            line(indent + 1, std::string("if(!full && (") + (extra == 1u ? "true" : "loEnd < upStart") + "))");
+            line(indent + 1, std::string(coldMerges ? "if(PTB_LIKELY(!full && (" : "if((!full && (") + (extra == 1u ? "true" : "loEnd < upStart") + ")))");
             line(indent + 1, "{");
             line(indent + 2, "planeFinish(loEnd, upStart, loTags, upTags, full, hit, two, lt0, lt1, ut0, ltags, utags);");
             line(indent + 2, var(id) + " = rlCluster(ev, hit, two, lt0, lt1, ut0, ltags, utags);");
@@ -676,10 +690,11 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
         int nLeaves = 0;
         for(const FastTreeItem &it : tree.items)
             nLeaves += it.kind == PTB_OP_PUSH_PRIM;
+        // (PTB_SPEC_COLD=0 / 1: operators inline / through the one out-of-line merge whatever the size)
+        g.coldMerges = getenv("PTB_SPEC_COLD") ? atoi(getenv("PTB_SPEC_COLD")) != 0 : nLeaves >= 24;
         if(mode != 0 && (mode == 1 || nLeaves >= 24))
         {
             g.indexRunBounds();
-            g.coldMerges = !getenv("PTB_SPEC_COLD") || atoi(getenv("PTB_SPEC_COLD")) != 0;
             g.computeShapes();
             g.chooseShapes(root, mode == 1 ? 3 : 4);
         }
@@ -736,6 +751,8 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
     }
     else
         s += "__device__ __forceinline__ void specStageTable(uint32_t) {}\n";
+    if(g.usesBounds)
+        s += "// PTB_SPEC_BOUNDED_CALLS: shape-function calls of camera rays are guarded by bounding-sphere votes\n";
     for(const std::string &f : g.fnDefs)
         s += f;
     s += g.s;
