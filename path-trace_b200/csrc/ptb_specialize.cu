@@ -424,6 +424,7 @@ struct Gen
     // bounded, a Difference its left one, an Intersection either.
     std::map<size_t, uint4> runBound; // header word of a transformed-sphere leaf -> its bounding-sphere word
     int divergent = 0;                // > 0: the code being emitted runs under a per-lane condition
+    bool likelyHints = false;         // __builtin_expect on the plane clusters' register form (PTB_SPEC_HINTS=0: none)
     bool coldMerges = false;          // large programs: operators call ONE out-of-line merge (rlMergeSlow, ptb_csg_reg.cuh)
     bool usesBounds = false;
     void indexRunBounds()
@@ -515,6 +516,38 @@ struct Gen
         line(indent + 1, "if(" + L + ".n >= 2)");
         line(indent + 2, "ev.top += " + L + ".n;");
         line(indent, "}");
+    }
+
+    // ---- cold blocks ---------------------------------------------------------------------------------------------
+    // A plane cluster whose half-lines cross (or a ray lying in one of its planes) is merged leaf by leaf like any
+    // other subtree: a hundred instructions per plane that a render hardly ever executes, in the middle of the code
+    // every ray runs.  PTB_SPEC_COLD_BLOCKS=1 moves them to functions of their own behind the evaluator.  Off by
+    // default — measured on B200 (tools/gpu_r02I.sh): C5 bounce trace 86.7 / 86.7 / 92.5 ms per frame against 89.4,
+    // C4 camera trace 332 against 309, C3 8.93 against 9.35 Grays/s: within what the placement of a module in memory
+    // does to these kernels from one process to the next (C5 bounce trace: 89 or 100 ms, same code, same box).
+    bool coldBlocks = false;
+    std::vector<std::string> coldDefs;
+    int coldCluster(int id)
+    {
+        const int c = (int)coldDefs.size();
+        coldDefs.push_back(std::string());
+        std::string keep;
+        keep.swap(s);
+        s += "template <bool O0>\nstatic __device__ __noinline__ RMerged ptbCold" + std::to_string(c) +
+             "(uint32_t poolBase, int cap, int top, float ox, float oy, float oz, float dx, float dy, float dz)\n{\n";
+        line(1, "REval ev;");
+        line(1, "ev.poolBase = poolBase, ev.cap = cap, ev.top = top, ev.ovf = false, ev.tab = 0u;");
+        line(1, "const V3 o = mk(ox, oy, oz), d = mk(dx, dy, dz);");
+        divergent++;
+        node(id, 1, false, true); // declares L<id>_sub
+        divergent--;
+        line(1, "RMerged r;");
+        line(1, "r.L = L" + std::to_string(id) + "_sub, r.top = ev.top, r.ovf = ev.ovf;");
+        line(1, "return r;");
+        s += "}\n";
+        coldDefs[c] = s;
+        s.swap(keep);
+        return c;
     }
 
     // code of one plane record -> RList (a single plane, or the planes of a cluster folded in registers)
@@ -619,17 +652,26 @@ struct Gen
             line(indent, "RList " + var(id) + ";");
             line(indent, "{");
             planeFoldCalls(indent + 1, w, extra);
-            line(indent + 1, std::string(coldMerges ? "if(PTB_LIKELY(!full && (" : "if((!full && (") + (extra == 1u ? "true" : "loEnd < upStart") + ")))");
+            line(indent + 1, std::string(likelyHints ? "if(PTB_LIKELY(!full && (" : "if((!full && (") + (extra == 1u ? "true" : "loEnd < upStart") + ")))");
             line(indent + 1, "{");
             line(indent + 2, "planeFinish(loEnd, upStart, loTags, upTags, full, hit, two, lt0, lt1, ut0, ltags, utags);");
             line(indent + 2, var(id) + " = rlCluster(ev, hit, two, lt0, lt1, ut0, ltags, utags);");
             line(indent + 1, "}");
             line(indent + 1, "else");
             line(indent + 1, "{");
-            divergent++;
-            node(id, indent + 2, false, true); // declares L<id>_sub
-            divergent--;
-            line(indent + 2, "L" + std::to_string(id) + " = L" + std::to_string(id) + "_sub;");
+            if(!inFn && coldBlocks)
+            { // (hardly ever taken and as long as the rest of a small scene's code: out of line, see coldCluster)
+                const int c = coldCluster(id);
+                line(indent + 2, "const RMerged r_ = ptbCold" + std::to_string(c) + "<O0>(ev.poolBase, ev.cap, ev.top, o.x, o.y, o.z, d.x, d.y, d.z);");
+                line(indent + 2, "L" + std::to_string(id) + " = r_.L, ev.top = r_.top, ev.ovf = ev.ovf || r_.ovf;");
+            }
+            else
+            {
+                divergent++;
+                node(id, indent + 2, false, true); // declares L<id>_sub
+                divergent--;
+                line(indent + 2, "L" + std::to_string(id) + " = L" + std::to_string(id) + "_sub;");
+            }
             line(indent + 1, "}");
             line(indent, "}");
             return;
@@ -692,6 +734,8 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
             nLeaves += it.kind == PTB_OP_PUSH_PRIM;
         // (PTB_SPEC_COLD=0 / 1: operators inline / through the one out-of-line merge whatever the size)
         g.coldMerges = getenv("PTB_SPEC_COLD") ? atoi(getenv("PTB_SPEC_COLD")) != 0 : nLeaves >= 24;
+        g.likelyHints = getenv("PTB_SPEC_HINTS") ? atoi(getenv("PTB_SPEC_HINTS")) != 0 : g.coldMerges;
+        g.coldBlocks = getenv("PTB_SPEC_COLD_BLOCKS") && atoi(getenv("PTB_SPEC_COLD_BLOCKS")) != 0;
         if(mode != 0 && (mode == 1 || nLeaves >= 24))
         {
             g.indexRunBounds();
@@ -714,12 +758,22 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
         { // the root Union is scanned while it is merged; its right operand (a leaf or a plane cluster) stays in registers
             g.node(rn.left, 1);
             g.rootRight(rn.right, 1);
-            g.line(1, "if(nB >= 0)");
+            g.line(1, g.likelyHints ? "if(PTB_LIKELY(nB >= 0))" : "if(nB >= 0)");
             g.line(2, "return rlUnionFirstHit(ev, " + g.var(rn.left) + ", nB, b0, b1, t, tag);");
             if(g.isCluster(rn.right) && prog[(size_t)tree.items[g.nodes[rn.right].firstItem].clusterWord].z >= 2u)
             { // a cluster of three or more planes whose half-lines cross: its leaves one by one, then the root as a list
-                g.node(rn.right, 1, false);
-                g.line(1, "const RList Lroot = rlUnion(ev, " + g.var(rn.left) + ", " + "L" + std::to_string(rn.right) + "_sub);");
+                if(g.coldBlocks)
+                {
+                    const int c = g.coldCluster(rn.right);
+                    g.line(1, "const RMerged r_ = ptbCold" + std::to_string(c) + "<O0>(ev.poolBase, ev.cap, ev.top, o.x, o.y, o.z, d.x, d.y, d.z);");
+                    g.line(1, "ev.top = r_.top, ev.ovf = ev.ovf || r_.ovf;");
+                    g.line(1, "const RList Lroot = rlUnion(ev, " + g.var(rn.left) + ", r_.L);");
+                }
+                else
+                {
+                    g.node(rn.right, 1, false);
+                    g.line(1, "const RList Lroot = rlUnion(ev, " + g.var(rn.left) + ", " + "L" + std::to_string(rn.right) + "_sub);");
+                }
                 g.line(1, "return rlFirstHit(ev, Lroot, t, tag);");
             }
             else
@@ -754,6 +808,8 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
     if(g.usesBounds)
         s += "// PTB_SPEC_BOUNDED_CALLS: shape-function calls of camera rays are guarded by bounding-sphere votes\n";
     for(const std::string &f : g.fnDefs)
+        s += f;
+    for(const std::string &f : g.coldDefs)
         s += f;
     s += g.s;
     s += "} // namespace ptb\n";

@@ -33,7 +33,7 @@ def emulate(tmp_path, name, flat, rays_o, rays_d, origin0, cap=12):
     d.mkdir(exist_ok=True)
     (d / "trace.inc").write_text(functions_only(probe_text(flat, 0)))
     # (both modules carry their own copy of the constant table and the shape functions: one program here, so rename)
-    (d / "list.inc").write_text(functions_only(probe_text(flat, 1)).replace("ptbTab", "ptbTabList").replace("ptbShape", "ptbShapeList").replace("specStageTable", "specStageTableList"))
+    (d / "list.inc").write_text(functions_only(probe_text(flat, 1)).replace("ptbTab", "ptbTabList").replace("ptbShape", "ptbShapeList").replace("ptbCold", "ptbColdList").replace("specStageTable", "specStageTableList"))
     (d / "prog.hex").write_text(probe_text(flat, 2))
     rays = np.concatenate([np.asarray(rays_o, np.float32).reshape(-1, 3), np.asarray(rays_d, np.float32).reshape(-1, 3)], 1)
     rays.tofile(d / "rays.bin")
