@@ -388,6 +388,47 @@ __device__ __forceinline__ void rlMergeCold(REval &ev, int kind, RList &A, const
     const RMerged r = rlMergeSlow(kind, ev.poolBase, ev.cap, ev.top, A, B);
     A = r.L, ev.top = r.top, ev.ovf = ev.ovf || r.ovf;
 }
+// A leaner form of the same: only the closed forms of two single spans go out of line, as ONE function with scalar
+// parameters and a uint4 result (registers both ways): {n | overflow << 31, t0, t1, tags}; a result of two spans
+// lies in pool slots [top, top + 2).  Lists of two or more spans take rlGeneral (whose merge is out of line already).
+static __device__ __noinline__ uint4 rlMerge11Call(int kind, uint32_t poolBase, int cap, int top, float a0, float a1, uint32_t at, float b0, float b1, uint32_t bt)
+{
+    REval ev;
+    ev.poolBase = poolBase, ev.cap = cap, ev.top = top, ev.ovf = false, ev.tab = 0u;
+    const SpanRec A = rlSpan(a0, a1, at), B = rlSpan(b0, b1, bt);
+    const RList r = kind == DK_UNION ? rlUnion11(ev, A, B) : rlDifference11(ev, A, B);
+    return make_uint4((uint32_t)r.n | (ev.ovf ? 0x80000000u : 0u), __float_as_uint(r.a.t0), __float_as_uint(r.a.t1), r.a.tags);
+}
+__device__ __forceinline__ void rlMerge11(REval &ev, int kind, RList &A, const RList &B)
+{
+    const uint4 r = rlMerge11Call(kind, ev.poolBase, ev.cap, ev.top, A.a.t0, A.a.t1, A.a.tags, B.a.t0, B.a.t1, B.a.tags);
+    A.n = (int)(r.x & 0x7FFFFFFFu), A.a = rlSpan(__uint_as_float(r.y), __uint_as_float(r.z), r.w), A.base = ev.top;
+    ev.ovf = ev.ovf || (r.x >> 31) != 0u;
+    if(A.n >= 2)
+        ev.top += 2;
+}
+__device__ __forceinline__ void rlUnionIntoLean(REval &ev, RList &A, const RList &B)
+{
+    if(B.n == 0)
+        return;
+    if(A.n == 0)
+        A = B;
+    else if(A.n == 1 && B.n == 1)
+        rlMerge11(ev, DK_UNION, A, B);
+    else
+        A = rlGeneral(ev, DK_UNION, A, B);
+}
+__device__ __forceinline__ void rlDifferenceIntoLean(REval &ev, RList &A, const RList &B)
+{
+    if(B.n == 0 || A.n == 0)
+        return;
+    if(A.n == 1 && B.n == 1)
+        rlMerge11(ev, DK_DIFFERENCE, A, B);
+    else
+        A = rlGeneral(ev, DK_DIFFERENCE, A, B);
+}
+__device__ __forceinline__ void rlIntersectionIntoLean(REval &ev, RList &A, const RList &B) { rlIntersectionInto(ev, A, B); } // (its closed form pushes nothing and is short)
+
 // (PTB_UNLIKELY: the merge proper goes to the end of the function, out of the way of the code every ray runs)
 #ifdef PTB_HOST_EMU
 #define PTB_UNLIKELY(x) (x)

@@ -425,6 +425,7 @@ struct Gen
     std::map<size_t, uint4> runBound; // header word of a transformed-sphere leaf -> its bounding-sphere word
     int divergent = 0;                // > 0: the code being emitted runs under a per-lane condition
     bool likelyHints = false;         // __builtin_expect on the plane clusters' register form (PTB_SPEC_HINTS=0: none)
+    bool leanMerges = false;          // small programs: only the closed forms of two single spans out of line (rlMerge11Call)
     bool coldMerges = false;          // large programs: operators call ONE out-of-line merge (rlMergeSlow, ptb_csg_reg.cuh)
     bool usesBounds = false;
     void indexRunBounds()
@@ -694,7 +695,7 @@ struct Gen
         }
         const std::string rhs = kind == PTB_OP_UNION ? var(n.right) : "L" + std::to_string(n.right) + "_r";
         const char *fn = kind == PTB_OP_UNION ? "rlUnionInto" : kind == PTB_OP_DIFFERENCE ? "rlDifferenceInto" : "rlIntersectionInto";
-        line(indent, std::string(fn) + (coldMerges ? "Cold" : "") + "(ev, " + var(n.left) + ", " + rhs + ");");
+        line(indent, std::string(fn) + (coldMerges ? "Cold" : leanMerges ? "Lean" : "") + "(ev, " + var(n.left) + ", " + rhs + ");");
         if(asCluster)
             alias[id] = n.left; // from here on this node's list IS the left operand's variable
         else
@@ -732,8 +733,12 @@ static std::string specializeSourceGen2(const std::vector<uint4> &prog, const Fa
         int nLeaves = 0;
         for(const FastTreeItem &it : tree.items)
             nLeaves += it.kind == PTB_OP_PUSH_PRIM;
-        // (PTB_SPEC_COLD=0 / 1: operators inline / through the one out-of-line merge whatever the size)
-        g.coldMerges = getenv("PTB_SPEC_COLD") ? atoi(getenv("PTB_SPEC_COLD")) != 0 : nLeaves >= 24;
+        // PTB_SPEC_COLD=0 / 1 / 2: operators inline / through the one out-of-line merge / closed forms of two single
+        // spans out of line, whatever the size.  Measured on B200 (tools/gpu_r02J.sh, ms per frame): C5 bounce trace
+        // inline 89.4 / 100.3 / 89.5 in three processes (the placement of the module decides), lean 92.0 / 92.2 / 91.9,
+        // cold 97; C3 9.33 -> 10.04 Grays/s lean; C4 camera trace cold 313, lean 337.
+        g.coldMerges = getenv("PTB_SPEC_COLD") ? atoi(getenv("PTB_SPEC_COLD")) == 1 : nLeaves >= 24;
+        g.leanMerges = getenv("PTB_SPEC_COLD") ? atoi(getenv("PTB_SPEC_COLD")) == 2 : !g.coldMerges;
         g.likelyHints = getenv("PTB_SPEC_HINTS") ? atoi(getenv("PTB_SPEC_HINTS")) != 0 : g.coldMerges;
         g.coldBlocks = getenv("PTB_SPEC_COLD_BLOCKS") && atoi(getenv("PTB_SPEC_COLD_BLOCKS")) != 0;
         if(mode != 0 && (mode == 1 || nLeaves >= 24))

@@ -24,7 +24,7 @@ def test_generated_source_compiles_for_sm100a():
     for world, which in ((scenes.config5(b), 0), (scenes.config3(b), 1), (scenes.random_tree(b, 7, 9), 0)):
         flat = device.Flat(world)
         source, cubin = device.specialize_probe(flat, which)
-        assert ("specTrace" if which == 0 else "specList") in source and "rlUnionInto(ev, " in source and "ptb_csg_reg.cuh" in source
+        assert ("specTrace" if which == 0 else "specList") in source and "rlUnionIntoLean(ev, " in source and "ptb_csg_reg.cuh" in source
         assert ("ptbSpecTracePrimary" in source) == (which == 0) and ("ptbSpecIntersectO0" in source) == (which == 1)
         assert cubin > 10000
     # every leaf of the tree has its code: the eight isomorphic groups of config 4 (six transformed spheres cut by
