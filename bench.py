@@ -512,9 +512,9 @@ def run_ours(args):
         for k, v in enumerate((t_b - t_a, t_c - t_b, t_d - t_c)):
             e2e_parts[k] += v * 1e3 / e2e_steps
         if os.environ.get("PTB200_E2E_DEBUG"):
-            print("e2e step: create %.1f render+download %.1f destroy %.1f ms" % ((t_b - t_a) * 1e3, (t_c - t_b) * 1e3, (t_d - t_c) * 1e3), file=sys.stderr)
+            print("e2e step (rank %d): create %.1f render+download %.1f destroy %.1f ms" % (rank, (t_b - t_a) * 1e3, (t_c - t_b) * 1e3, (t_d - t_c) * 1e3), file=sys.stderr)
 
-    for _ in range(2):  # warm-up: the first scene of a process allocates the queues (GBs) and image arrays that later ones reuse
+    for _ in range(3):  # warm-up (W >= 3): the first scenes of a process allocate the queues (GBs), image arrays and NCCL buffers that later ones reuse (8 GPUs: create 100, 27, 14, then 7 ms)
         e2e_step()
     e2e_parts[:] = [0.0, 0.0, 0.0]
     barrier()
