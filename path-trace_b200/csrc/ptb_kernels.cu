@@ -14,6 +14,27 @@
 
 #include <stdlib.h>
 
+#include <map>
+#include <mutex>
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per kernel and device and only ever has to GROW: set it when a
+// launch needs more than any before it, not at every launch (512 trace launches per C4 frame).
+template <class K>
+static void ensureDynamicSmem(K kernel, size_t bytes)
+{
+    static std::mutex lock;
+    static std::map<std::pair<const void *, int>, size_t> have;
+    int device = 0;
+    cudaGetDevice(&device);
+    std::lock_guard<std::mutex> g(lock);
+    size_t &h = have[std::make_pair((const void *)kernel, device)];
+    if(bytes > h)
+    {
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        h = bytes;
+    }
+}
+
 #include "ptb_launch.h"
 #include "ptb_trace.cuh"
 #include "ptb_shade.cuh"
@@ -121,13 +142,13 @@ void launchIntersect(const DevScene &sc, const CsgConfig &cfg, const float4 *ori
 {
     if(exact)
     {
-        cudaFuncSetAttribute(intersectExactKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        ensureDynamicSmem(intersectExactKernel, cfg.smemBytes);
         intersectExactKernel<<<cfg.blocks, cfg.threads, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.stageProgram, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans, maxSpans);
     }
     else
     {
 #define PTB_LAUNCH_INTERSECT(GP, O0)                                                                                                                                      \
-    cudaFuncSetAttribute(intersectFastKernel<GP, O0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);                                                   \
+    ensureDynamicSmem(intersectFastKernel<GP, O0>, cfg.smemBytes);                                                   \
     intersectFastKernel<GP, O0><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, origins, dirs, n, hits, spans, maxSpans)
         if(cfg.stageProgram && origin0)
         {
@@ -422,12 +443,12 @@ int tailBlocksPerSm(bool globalProgram, size_t smemBytes)
     cudaError_t e;
     if(globalProgram)
     {
-        cudaFuncSetAttribute(tailKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+        ensureDynamicSmem(tailKernel<true>, smemBytes);
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, tailKernel<true>, PTB_FAST_THREADS, smemBytes);
     }
     else
     {
-        cudaFuncSetAttribute(tailKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+        ensureDynamicSmem(tailKernel<false>, smemBytes);
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, tailKernel<false>, PTB_FAST_THREADS, smemBytes);
     }
     if(e != cudaSuccess)
@@ -442,12 +463,12 @@ void launchTracePrimary(const DevScene &sc, const CsgConfig &cfg, const RenderPa
 {
     if(cfg.stageProgram)
     {
-        cudaFuncSetAttribute(tracePrimaryKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        ensureDynamicSmem(tracePrimaryKernel<false>, cfg.smemBytes);
         tracePrimaryKernel<false><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, pass, hits);
     }
     else
     {
-        cudaFuncSetAttribute(tracePrimaryKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        ensureDynamicSmem(tracePrimaryKernel<true>, cfg.smemBytes);
         tracePrimaryKernel<true><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, pass, hits);
     }
 }
@@ -455,12 +476,12 @@ void launchTraceQueue(const DevScene &sc, const CsgConfig &cfg, RayQueue in, con
 {
     if(cfg.stageProgram)
     {
-        cudaFuncSetAttribute(traceQueueKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        ensureDynamicSmem(traceQueueKernel<false>, cfg.smemBytes);
         traceQueueKernel<false><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, in, inCount, hits);
     }
     else
     {
-        cudaFuncSetAttribute(traceQueueKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smemBytes);
+        ensureDynamicSmem(traceQueueKernel<true>, cfg.smemBytes);
         traceQueueKernel<true><<<cfg.blocks, PTB_FAST_THREADS, cfg.smemBytes, stream>>>(sc, cfg.cap, cfg.overflow, cfg.ovfStride, in, inCount, hits);
     }
 }
@@ -859,7 +880,7 @@ template <class K>
 static int occupancyOf(K kernel, int threads, size_t smemBytes)
 {
     int n = 0;
-    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    ensureDynamicSmem(kernel, smemBytes);
     if(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, smemBytes) != cudaSuccess)
     {
         cudaGetLastError();
