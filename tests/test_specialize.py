@@ -177,3 +177,37 @@ def test_run_bounding_spheres_enclose_their_leaves():
         else:
             w += 1
     assert runs == 8
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("order", ["pixel", "random"])
+def test_bounding_spheres_change_no_span(order, monkeypatch):
+    """The interpreter's bounding-sphere votes (camera rays: PTB_FLAG_ORIGIN0) only skip leaves that would have
+    missed: hits and whole span lists of config 4 are bit-identical with (default) and without (PTB_FAST_BOUNDS=0,
+    read when the scene is created) the spheres — for rays in pixel order, where a warp covers a few pixels and whole
+    runs are skipped, and in random order, where single leaves are."""
+    b = product_builder()
+    w, h = 1024, 576
+    ys, xs = np.mgrid[0:h, 0:w]
+    rs = np.random.RandomState(12)
+    px = (xs + rs.rand(h, w)).reshape(-1) * (3840.0 / w)
+    py = (ys + rs.rand(h, w)).reshape(-1) * (2160.0 / h)
+    d = np.stack([(px * 2 / 3840.0 - 1) * 3840.0, (1 - py * 2 / 2160.0) * 2160.0, np.full(px.shape, -4320.0)], 1).astype(np.float32)
+    if order == "random":
+        d = d[rs.permutation(len(d))]
+    o = np.zeros_like(d)
+    flat = device.Flat(scenes.config4(b))
+    with_bounds = device.DeviceScene(flat)
+    monkeypatch.setenv("PTB_FAST_BOUNDS", "0")
+    without = device.DeviceScene(flat)
+    monkeypatch.delenv("PTB_FAST_BOUNDS")
+    h1, s1 = with_bounds.intersect(o, d, 8, capi.PTB_FLAG_ORIGIN0 | INTERP)
+    h0, s0 = without.intersect(o, d, 8, capi.PTB_FLAG_ORIGIN0 | INTERP)
+    assert h0.tobytes() == h1.tobytes() and s0.tobytes() == s1.tobytes()
+    on_sphere = (h0["kind"] != 0) & (h0["prim"] < 64) & (h0["prim"] % 8 < 6)
+    assert 0.05 < on_sphere.mean() < 0.9  # the spheres are what a good part of the rays see first, and not all
+    # and the scene without them really has none: its program is 48 words shorter
+    text1, _ = device.specialize_probe(flat, 2, compile=False)
+    monkeypatch.setenv("PTB_FAST_BOUNDS", "0")
+    text0, _ = device.specialize_probe(flat, 2, compile=False)
+    assert len(text1.split()) - len(text0.split()) == 48 * 4
