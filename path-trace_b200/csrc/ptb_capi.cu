@@ -118,13 +118,8 @@ void DeviceBuffer::release()
 {
     if(p)
     {
-        if(bytes >= (1u << 20))
-        {
-            std::lock_guard<std::mutex> g(g_cacheLock);
-            g_cache.push_back(CachedBlock{p, bytes, device});
-        }
-        else
-            cudaFree(p);
+        std::lock_guard<std::mutex> g(g_cacheLock);
+        g_cache.push_back(CachedBlock{p, bytes, device});
     }
     p = nullptr, bytes = 0;
 }
@@ -133,6 +128,7 @@ cudaError_t DeviceBuffer::ensure(size_t n)
     if(n <= bytes)
         return cudaSuccess;
     release();
+    n = std::max<size_t>(n, size_t(1) << 20); // small blocks too go through the cache: a cudaMalloc / cudaFree pair per scene and buffer stalls for up to 100 ms now and then in a process that holds > 100 GB
     cudaError_t e = cudaGetDevice(&device);
     if(e != cudaSuccess)
         return e;
@@ -164,10 +160,45 @@ cudaError_t DeviceBuffer::ensure(size_t n)
     return e;
 }
 
+// Pinned host blocks for the per-level counters a stats call reads back: kept per process like the device blocks
+// (cudaMallocHost / cudaFreeHost per scene are synchronising calls).
+static std::vector<std::pair<unsigned *, size_t>> g_hostCounterCache;
+static unsigned *hostCountersGet(size_t n, size_t &got)
+{
+    {
+        std::lock_guard<std::mutex> g(g_cacheLock);
+        for(size_t i = 0; i < g_hostCounterCache.size(); i++)
+            if(g_hostCounterCache[i].second >= n)
+            {
+                unsigned *p = g_hostCounterCache[i].first;
+                got = g_hostCounterCache[i].second;
+                g_hostCounterCache[i] = g_hostCounterCache.back();
+                g_hostCounterCache.pop_back();
+                return p;
+            }
+    }
+    unsigned *p = nullptr;
+    got = std::max<size_t>(n, 4096);
+    if(cudaMallocHost((void **)&p, got * sizeof(unsigned)) != cudaSuccess)
+    {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+static void hostCountersPut(unsigned *p, size_t n)
+{
+    std::lock_guard<std::mutex> g(g_cacheLock);
+    if(g_hostCounterCache.size() < 16)
+        g_hostCounterCache.push_back(std::make_pair(p, n));
+    else
+        cudaFreeHost(p);
+}
+
 RenderScratch::~RenderScratch()
 {
     if(hostCounters)
-        cudaFreeHost(hostCounters);
+        hostCountersPut(hostCounters, hostCountersLen);
     for(cudaEvent_t e : events)
         cudaEventDestroy(e);
 }
@@ -1782,10 +1813,13 @@ int ptb::renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbS
     if(sx.hostCountersLen < nCounters)
     {
         if(sx.hostCounters)
-            cudaFreeHost(sx.hostCounters);
-        sx.hostCounters = nullptr;
-        CU(cudaMallocHost((void **)&sx.hostCounters, nCounters * sizeof(unsigned)));
-        sx.hostCountersLen = nCounters;
+            hostCountersPut(sx.hostCounters, sx.hostCountersLen);
+        sx.hostCounters = hostCountersGet(nCounters, sx.hostCountersLen);
+        if(!sx.hostCounters)
+        {
+            sx.hostCountersLen = 0;
+            return fail(PTB_ENOMEM, "no page-locked host memory for the ray counters");
+        }
     }
     CU(cudaMemcpyAsync(sx.hostCounters, sx.counters.p, nCounters * sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
     CU(cudaStreamSynchronize(stream));
