@@ -1678,7 +1678,7 @@ int ptb::renderPasses(PtbScene *s, const PtbRenderParams *p, float4 *accum, PtbS
         perPass = (int)std::max<size_t>(1, want / nPix);
     }
     perPass = std::min(perPass, p->spp);
-    if((size_t)perPass * nPix > 0xFFFFFFF0ull)
+    if((size_t)perPass * nPix > 0xFF000000ull) // (the shade kernels add a grid stride of < 2^24 to a work index in 32 bits)
         return fail(PTB_EINVAL, "samples_per_pass x pixels exceeds the 32-bit queue index");
     // the last global sample index must fit the kernels' 32-bit sample counter
     if((long long)p->sample_offset + ((long long)p->spp - 1) * (long long)p->sample_stride > 0x7FFFFFFFll)

@@ -288,8 +288,9 @@ __global__ void __launch_bounds__(PTB_SHADE_THREADS, MINCTAS) shadeKernel(DevSce
                                                                  const unsigned *__restrict__ inCount, RayQueue out, unsigned *outCount)
 {
     const unsigned nPix = (unsigned)pass.rw * (unsigned)pass.rh;
-    const unsigned long long total = PRIMARY ? (unsigned long long)nPix * (unsigned)pass.samplesThisPass : (unsigned long long)*inCount;
-    const unsigned long long stride = (unsigned long long)gridDim.x * PTB_SHADE_THREADS;
+    // 32-bit work indices: the host keeps paths per pass below 2^32 - 2^24 (renderPasses) and a grid has < 2^24 threads
+    const unsigned total = PRIMARY ? nPix * (unsigned)pass.samplesThisPass : *inCount;
+    const unsigned stride = gridDim.x * PTB_SHADE_THREADS;
     __shared__ float4 stageAll[PTB_SHADE_THREADS / 32][4][64];
     float4(*stage)[64] = stageAll[threadIdx.x >> 5];
     const unsigned lane = threadIdx.x & 31u;
@@ -297,7 +298,7 @@ __global__ void __launch_bounds__(PTB_SHADE_THREADS, MINCTAS) shadeKernel(DevSce
     // software pipeline: the next trip's hit record (and queue record) is requested before this
     // trip is shaded, so its HBM latency hides behind the shading (ncu: 37-54 % of the stall samples
     // of this kernel were long-scoreboard waits on those loads)
-    const unsigned long long first = (unsigned long long)blockIdx.x * PTB_SHADE_THREADS + (threadIdx.x & ~31u);
+    const unsigned first = blockIdx.x * PTB_SHADE_THREADS + (threadIdx.x & ~31u);
     uint2 hNext = make_uint2(0u, 0u);
     float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0, n3 = n0;
     if(first + lane < total)
@@ -306,9 +307,9 @@ __global__ void __launch_bounds__(PTB_SHADE_THREADS, MINCTAS) shadeKernel(DevSce
         if(!PRIMARY)
             n0 = __ldcs(&in.q0[first + lane]), n1 = __ldcs(&in.q1[first + lane]), n2 = __ldcs(&in.q2[first + lane]), n3 = __ldcs(&in.q3[first + lane]);
     }
-    for(unsigned long long base = first; base < total; base += stride)
+    for(unsigned base = first; base < total; base += stride)
     {
-        unsigned long long i = base + lane;
+        const unsigned i = base + lane;
         bool alive = false;
         PathState ps;
         V3 rad = mk(0.f, 0.f, 0.f);
