@@ -394,12 +394,12 @@ __global__ void __launch_bounds__(PTB_FAST_THREADS) tailKernel(DevScene sc, int 
     if(total == 0u)
         return;
     FastCtx cx = setupFast<GP, 1>(sc, cap, overflow, ovfStride);
-    const unsigned long long stride = (unsigned long long)gridDim.x * PTB_FAST_THREADS;
+    const unsigned stride = gridDim.x * PTB_FAST_THREADS;
     const unsigned lane = threadIdx.x & 31u;
     unsigned extra = 0u;
-    for(unsigned long long base = (unsigned long long)blockIdx.x * PTB_FAST_THREADS + (threadIdx.x & ~31u); base < total; base += stride)
+    for(unsigned base = blockIdx.x * PTB_FAST_THREADS + (threadIdx.x & ~31u); base < total; base += stride)
     {
-        const unsigned long long i = base + lane;
+        const unsigned i = base + lane;
         bool alive = i < total;
         PathState ps;
         ps.o = ps.d = ps.thr = mk(0.f, 0.f, 0.f);

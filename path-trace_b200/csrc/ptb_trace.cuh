@@ -288,18 +288,19 @@ __device__ __forceinline__ void tracePrimaryBody(const DevScene &sc, int cap, fl
 {
     FastCtx cx = setupFast<GP, PTB_TRACE_RAYS>(sc, cap, overflow, ovfStride);
     const unsigned nPix = (unsigned)pass.rw * (unsigned)pass.rh;
-    const unsigned long long total = (unsigned long long)nPix * (unsigned)pass.samplesThisPass;
-    const unsigned long long stride = (unsigned long long)gridDim.x * PTB_FAST_THREADS * PTB_TRACE_RAYS;
+    // (32-bit work indices: the host keeps paths per pass below 2^32 - 2^24, a grid has < 2^24 threads)
+    const unsigned total = nPix * (unsigned)pass.samplesThisPass;
+    const unsigned stride = gridDim.x * PTB_FAST_THREADS * PTB_TRACE_RAYS;
     // warp-uniform trip count; idle lanes of the last warp carry a null ray
-    for(unsigned long long ctaBase = (unsigned long long)blockIdx.x * PTB_FAST_THREADS * PTB_TRACE_RAYS; ctaBase < total; ctaBase += stride)
+    for(unsigned ctaBase = blockIdx.x * PTB_FAST_THREADS * PTB_TRACE_RAYS; ctaBase < total; ctaBase += stride)
     {
-        const unsigned long long base = ctaBase + (unsigned long long)(threadIdx.x & ~31u) * PTB_TRACE_RAYS; // (a warp past the end carries null rays)
+        const unsigned base = ctaBase + (threadIdx.x & ~31u) * PTB_TRACE_RAYS; // (a warp past the end carries null rays)
         PTB_TRACE_TRIP_SYNC();
         V3 o[PTB_TRACE_RAYS], d[PTB_TRACE_RAYS];
 #pragma unroll
         for(int r = 0; r < PTB_TRACE_RAYS; r++)
         {
-            unsigned long long i = base + 32u * r + (threadIdx.x & 31u);
+            const unsigned i = base + 32u * r + (threadIdx.x & 31u);
             o[r] = d[r] = mk(0.f, 0.f, 0.f);
             if(i < total)
             {
@@ -313,7 +314,7 @@ __device__ __forceinline__ void tracePrimaryBody(const DevScene &sc, int cap, fl
 #pragma unroll
         for(int r = 0; r < PTB_TRACE_RAYS; r++)
         {
-            unsigned long long i = base + 32u * r + (threadIdx.x & 31u);
+            const unsigned i = base + 32u * r + (threadIdx.x & 31u);
             if(i < total)
                 __stcs(&hits[i], h[r]);
         }
@@ -328,16 +329,16 @@ __device__ __forceinline__ void traceQueueBody(const DevScene &sc, int cap, floa
     if(total == 0u)
         return;
     FastCtx cx = setupFast<GP, PTB_TRACE_RAYS>(sc, cap, overflow, ovfStride);
-    const unsigned long long stride = (unsigned long long)gridDim.x * PTB_FAST_THREADS * PTB_TRACE_RAYS;
-    for(unsigned long long ctaBase = (unsigned long long)blockIdx.x * PTB_FAST_THREADS * PTB_TRACE_RAYS; ctaBase < total; ctaBase += stride)
+    const unsigned stride = gridDim.x * PTB_FAST_THREADS * PTB_TRACE_RAYS;
+    for(unsigned ctaBase = blockIdx.x * PTB_FAST_THREADS * PTB_TRACE_RAYS; ctaBase < total; ctaBase += stride)
     {
-        const unsigned long long base = ctaBase + (unsigned long long)(threadIdx.x & ~31u) * PTB_TRACE_RAYS; // (a warp past the end carries null rays)
+        const unsigned base = ctaBase + (threadIdx.x & ~31u) * PTB_TRACE_RAYS; // (a warp past the end carries null rays)
         PTB_TRACE_TRIP_SYNC();
         V3 o[PTB_TRACE_RAYS], d[PTB_TRACE_RAYS];
 #pragma unroll
         for(int r = 0; r < PTB_TRACE_RAYS; r++)
         {
-            unsigned long long i = base + 32u * r + (threadIdx.x & 31u);
+            const unsigned i = base + 32u * r + (threadIdx.x & 31u);
             o[r] = d[r] = mk(0.f, 0.f, 0.f);
             if(i < total)
             {
@@ -350,7 +351,7 @@ __device__ __forceinline__ void traceQueueBody(const DevScene &sc, int cap, floa
 #pragma unroll
         for(int r = 0; r < PTB_TRACE_RAYS; r++)
         {
-            unsigned long long i = base + 32u * r + (threadIdx.x & 31u);
+            const unsigned i = base + 32u * r + (threadIdx.x & 31u);
             if(i < total)
                 __stcs(&hits[i], h[r]);
         }
