@@ -237,7 +237,9 @@ int ptb200_trim(void);
  * Limits (PTB_EINVAL beyond them; the reference has none): at most 32767 primitives (boundary tags are 16 bits)
  * and at most 32 pending operands on the evaluator's stack — a balanced tree of any size fits (unionArray,
  * src/test.cpp:52-64, needs log2 n), a right-deep chain `new Union(a, new Union(b, ...))` of more than 32
- * objects does not: build it left-deep or balanced (Union is the same set either way). */
+ * objects does not: build it left-deep or balanced (Union is the same set either way).
+ * Image pixels that lie in page-locked host memory (cudaHostAlloc / cudaHostRegister) are DMA-ed from there;
+ * pageable ones are staged through the library's own pinned buffer (slower, and a CPU copy). */
 int ptb200_scene_create(const PtbSceneDesc *desc, PtbScene **out);
 void ptb200_scene_destroy(PtbScene *scene);
 /* Appends an image after create (texops may name images not yet uploaded at create time). */
